@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- time-to-solution of the FP64 one-sided Jacobi SVD (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl svdj|reference] [--n 4096]
+
+A "step" is one full solve (sweeps to convergence, sigma/U/V out) of the synthetic workload.
+At N=1 the workload is BASELINE.json configs[1]: 4096 x 4096 dense uniform(0,1) FP64.
+
+Keys of the JSON line (one line, rank 0):
+  value      device-resident time-to-solution in seconds (inputs already in HBM; svdj_dgesvd_device)
+  e2e        the same solve through svdj_dgesvd with HOST buffers: H2D of A and D2H of U, s, V inside
+  roofline   HBM roofline of the dominant kernel (the fused level-1 step): algorithmic bytes
+             (32(m+n) per rotated pair, 16m per pair only tested) / CUDA-event time of the sweep loop
+  cpu_baseline  the oracle (kind "port") timed on this box's host cores on a bounded sample
+--impl reference times the reference's own solver (oracle/_ref/libref_cpu.so: main.cu built for the
+host, rotation kernel body run on CPU cores) -- one reference sweep per step, extrapolated to the
+sweeps a converged solve needs.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "svd_time_to_solution"
+UNIT = "s"
+# sweeps the reference's algorithm (its ordering, relative test tol = m*2^-53) needs on the bench input;
+# measured by the CUDA arm, equal to the oracle's count wherever the oracle is cheap enough to run.
+SWEEPS_TO_CONVERGE = {512: 13, 1024: 14, 2048: 15, 4096: 15, 8192: 16, 16384: 17}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smmax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smmax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smmax) if smmax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def algorithmic_bytes(m, n, tested, applied):
+    return applied * 32.0 * (m + n) + (tested - applied) * 16.0 * m
+
+
+def cpu_baseline_port(A0, sweeps_needed, budget_s=15.0):
+    """Oracle on host cores: time whole round-robin steps of sweep 1 until ~budget_s, extrapolate."""
+    import helpers as H
+
+    m, n = A0.shape
+    cores = os.cpu_count() or 1
+    A = A0.copy(order="F")
+    V = np.asfortranarray(np.eye(n))
+    steps = H.oracle_lib().oracle_num_steps(n)
+    o = H.OracleOpts(H.ORACLE_REL, m * 2.0 ** -53, 1, 0, cores, 0)
+    st = H.OracleStats()
+    t0 = time.perf_counter()
+    done = 0
+    while done < steps and (time.perf_counter() - t0) < budget_s:
+        H.oracle_lib().oracle_step(m, n, A, m, V, n, 1, done, C.byref(o), C.byref(st))
+        done += 1
+    dt = time.perf_counter() - t0
+    per_step = dt / max(done, 1)
+    value = per_step * steps * sweeps_needed
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{done} of {steps} round-robin steps of sweep 1 on {m}x{n} in {dt:.1f} s, "
+                      f"extrapolated x{steps}/{done} steps x{sweeps_needed} sweeps",
+            "rotations_per_s": (st.applied / dt) if dt > 0 else None}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own solver on host cores, one sweep (its maxIterations=1) per step."""
+    import helpers as H
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n = args.n
+    cores = os.cpu_count() or 1
+    sweeps_needed = SWEEPS_TO_CONVERGE.get(n, 15)
+    A0 = H.uniform_matrix(n, n, seed=n)
+    lib = H.ref_cpu_lib()
+    kind = "reference" if lib is not None else "port"
+    # bound the sample: a reference sweep at n=4096 costs tens of seconds on a few cores
+    n_sample = n
+    times = []
+
+    def one_sweep():
+        t0 = time.perf_counter()
+        if lib is not None:
+            H.ref_cpu_svd(A0 if n_sample == n else A0[:n_sample, :n_sample], sweeps=1, nthreads=cores)
+        else:
+            H.oracle_svd(A0, mode=H.ORACLE_ABS, threshold=1e-16, max_sweeps=1, sort_desc=0, nthreads=cores)
+        return time.perf_counter() - t0
+
+    t_first = one_sweep()  # counts as warm-up 1
+    budget = 240.0
+    total_calls = args.warmup + args.steps
+    if t_first * total_calls > budget:
+        # too slow for the whole run: keep this one measurement as every step's value
+        times = [t_first]
+    else:
+        for _ in range(max(args.warmup - 1, 0)):
+            one_sweep()
+        times = [one_sweep() for _ in range(args.steps)]
+    per_sweep = float(np.mean(times))
+    value = per_sweep * sweeps_needed
+    pairs = n * (n - 1) // 2
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": args.warmup, "ms_per_step": value * 1e3, "higher_is_better": False,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{n}x{n} dense uniform(0,1) FP64, full SVD (U, S, V)",
+                   "note": "reference runs exactly 1 sweep per call (main.cu:482); value = seconds per sweep x "
+                           f"{sweeps_needed} sweeps needed to converge"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{len(times)} x one reference sweep of {n}x{n} ({per_sweep:.2f} s each, "
+                                   f"{pairs} pairs), x{sweeps_needed} sweeps"},
+        "seconds_per_sweep": per_sweep,
+        "rotations_per_s": pairs / per_sweep,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_svdj(args):
+    import torch
+    import torch.distributed as dist
+
+    import helpers as H
+
+    svdj = importlib.import_module("svd-jacobi-mpi-cuda_b200")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    n = m = args.n
+    A0 = H.uniform_matrix(m, n, seed=n)
+    dA0 = torch.from_numpy(np.ascontiguousarray(A0.T)).cuda()  # column-major bytes
+    dA = torch.empty_like(dA0)
+    ds = torch.zeros(n, dtype=torch.float64, device="cuda")
+    dV = torch.empty(n, n, dtype=torch.float64, device="cuda")
+    opts = svdj.default_opts(variant=args.variant)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def solve_device():
+        dA.copy_(dA0)
+        return svdj.dgesvd_device(svdj.AllVec, svdj.AllVec, m, n, dA.data_ptr(), m, ds.data_ptr(), dV.data_ptr(), n,
+                                  opts, stream=stream)
+
+    for _ in range(args.warmup):
+        st = solve_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stats = []
+    ev0.record()
+    for _ in range(args.steps):
+        stats.append(solve_device())
+    ev1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    total_s = ev0.elapsed_time(ev1) * 1e-3
+    if world > 1:
+        t = torch.tensor([total_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_s = float(t.item())
+    per_step_s = total_s / args.steps
+
+    # roofline of the dominant kernel (the fused level-1 step), live from this run's CUDA events
+    last = stats[-1]
+    sweep_s = float(np.mean([s_.seconds_sweeps for s_ in stats]))
+    alg_bytes = float(np.mean([algorithmic_bytes(m, n, s_.tested, s_.applied) for s_ in stats]))
+    peak, peak_src = peaks()
+    achieved = alg_bytes / sweep_s / 1e9
+    launches_per_solve = last.step_kernel_launches
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "l1_pair_reg_kernel (fused Gram+rotation step)",
+                "frac_of_8TBps_nominal": achieved / 8000.0,
+                "alg_bytes_per_launch": alg_bytes / max(launches_per_solve, 1),
+                "avg_launch_us": sweep_s / max(launches_per_solve, 1) * 1e6}
+
+    # e2e: host buffers (pinned), H2D + solve + D2H inside the timed call
+    hA0 = torch.from_numpy(np.ascontiguousarray(A0.T)).pin_memory()
+    hA = torch.empty_like(hA0).pin_memory()
+    hs = torch.zeros(n, dtype=torch.float64).pin_memory()
+    hV = torch.empty(n, n, dtype=torch.float64).pin_memory()
+    e2e_times = []
+    for it in range(1 + args.steps):
+        hA.copy_(hA0)
+        barrier()
+        t0 = time.perf_counter()
+        st_h = svdj.Stats()
+        rc = svdj.lib.svdj_dgesvd(svdj.AllVec, svdj.AllVec, m, n, hA.data_ptr(), m, hs.data_ptr(), hV.data_ptr(), n,
+                                  C.byref(opts), C.byref(st_h))
+        assert rc == 0, svdj.last_error()
+        dt = time.perf_counter() - t0
+        if it > 0:
+            e2e_times.append(dt)
+    e2e_s = float(np.mean(e2e_times))
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+
+    if rank == 0:
+        # accuracy of the last e2e result (cheap, on the GPU) so that the line carries its own parity evidence
+        U = hA.cuda().T
+        V = hV.cuda().T
+        S = hs.cuda()
+        eye = torch.eye(n, dtype=torch.float64, device="cuda")
+        A0d = dA0.T
+        acc = {"orth_u": float((U.T @ U - eye).abs().max()), "orth_v": float((V.T @ V - eye).abs().max()),
+               "resid": float(torch.linalg.norm(A0d - (U * S) @ V.T) / torch.linalg.norm(A0d)),
+               "bound_10_n_eps": 10 * n * 2.0 ** -52}
+        del U, V, eye
+        cpu = cpu_baseline_port(A0, last.sweeps) if not args.no_cpu_baseline else None
+        pairs = n * (n - 1) // 2
+        line = {
+            "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False,
+            "scaling": "strong" if world == 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence",
+                       "variant": {1: "level1", 2: "block"}.get(last.variant, str(last.variant)),
+                       "tol": "m*2^-53 relative", "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20)
+                       if 2 * m * n * 8 > 126e6 else "inputs fit L2; restored from a master copy each step",
+                       "parallelism": "1 GPU" if world == 1 else f"{world} independent replicas"},
+            "sweeps": last.sweeps, "rotations_applied": last.applied, "pairs_tested": last.tested,
+            "rotations_per_s": last.tested / last.seconds_sweeps,
+            "seconds_sweeps": sweep_s, "seconds_finalize": last.seconds_finalize,
+            "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
+                    "d2h_bytes_per_step": (m * n + n * n + min(m, n)) * 8,
+                    "h2d_s": st_h.seconds_h2d, "d2h_s": st_h.seconds_d2h},
+            "gpu_launches": int(sum(s_.launches for s_ in stats)),
+            "clocks": clocks, "accuracy": acc,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="svdj", choices=["svdj", "reference"])
+    ap.add_argument("--n", type=int, default=4096)
+    ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_svdj(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,149 @@
+/*
+ * svdj.h -- C ABI of the B200-native one-sided Jacobi SVD (libsvdj.so).
+ *
+ * This is the drop-in boundary for the solver that the reference driver times
+ * (/root/reference/main.cu:1587 -> omp_mpi_cuda_dgesvd_local_matrices, main.cu:440-1423;
+ * single-process twin cuda_dgesvd_kernel, main.cu:163-437; declarations
+ * lib/JacobiMethods.cuh:44-62).  Plain pointers and sizes only: no C++ or torch types.
+ * The C++ shims with the reference's exact signatures live in svdj_reference_api.hpp.
+ *
+ * Data contract (same as the reference, lib/JacobiMethods.cuh:31-43, lib/global.cuh:14):
+ *   A   m x n, column-major, leading dimension lda >= m.  In: the matrix.  Out: U in place
+ *       (A[:,k] / sigma_k), or the un-normalised A*V when jobu == SVDJ_NOVEC.
+ *   s   min(m,n) doubles.  Out: singular values.
+ *   V   n x n, column-major, ldv >= n.  Out: V (not V^T), so that A = sum_k U[:,k] s[k] V[:,k]^T
+ *       (main.cu:1645-1647).  Untouched when jobv == SVDJ_NOVEC.
+ * Differences from the reference, all on the safe side: s and V need not be zero-filled by the
+ * caller (the reference requires it: lib/JacobiMethods.cu:1151, 213-226); sweeps repeat until
+ * convergence instead of exactly one (lib/JacobiMethods.cu:234); sigma comes back sorted in
+ * descending order with U and V permuted alike, as the reference's own doc block promises
+ * (lib/JacobiMethods.cu:22-23) -- set opts.sort_desc = 0 for the reference's raw order;
+ * every CUDA call is checked and failures come back as a status code (the reference ignores them).
+ *
+ * There is no CPU fallback: without a CUDA device every compute entry point returns
+ * SVDJ_ERR_CUDA.
+ */
+#ifndef SVDJ_H_
+#define SVDJ_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* lib/JacobiMethods.cuh:25-29 (enum SVD_OPTIONS) -- same numeric values */
+enum { SVDJ_ALLVEC = 0, SVDJ_SOMEVEC = 1, SVDJ_NOVEC = 2 };
+
+/* Which sweep implementation runs. */
+enum {
+  SVDJ_VARIANT_AUTO = 0,
+  SVDJ_VARIANT_LEVEL1 = 1, /* fused Gram + Givens rotation per column pair: HBM-bound (main.cu:450-510 in one pass) */
+  SVDJ_VARIANT_BLOCK = 2   /* block Jacobi: panel Gram, on-chip eigen-solve, panel update as FP64 tensor-core tiles */
+};
+
+/* How a pair decides whether it is rotated. */
+enum {
+  SVDJ_THRESH_REL = 0, /* |a_p.a_q| > tol * |a_p| |a_q|   (from the value computed at lib/JacobiMethods.cu:462) */
+  SVDJ_THRESH_ABS = 1  /* |a_p.a_q| > tol                 (the reference's test, lib/JacobiMethods.cu:466, 1271) */
+};
+
+/* Status codes.  0 = success; negative = argument number (1-based, as in LAPACK xerbla and as the
+ * reference's doc block describes, lib/JacobiMethods.cu:180-187); positive = run-time condition. */
+enum {
+  SVDJ_OK = 0,
+  SVDJ_NOT_CONVERGED = 1, /* max_sweeps reached; outputs hold the current iterate */
+  SVDJ_ERR_CUDA = 2,      /* a CUDA call failed or no device; see svdj_last_error() */
+  SVDJ_ERR_ALLOC = 3,     /* device or host allocation failed */
+  SVDJ_ERR_UNSUPPORTED = 4
+};
+
+typedef struct svdj_opts {
+  double tol;         /* <= 0: default m * 2^-53 (LAPACK dgesvj's choice) in REL mode, 1e-16 in ABS mode */
+  int max_sweeps;     /* <= 0: default 60.  The reference runs exactly 1 (lib/JacobiMethods.cu:234) */
+  int sort_desc;      /* 1: sigma descending, U/V columns permuted alike (default); 0: reference's raw column order */
+  int variant;        /* SVDJ_VARIANT_* */
+  int threshold_mode; /* SVDJ_THRESH_* */
+  int block;          /* block width for SVDJ_VARIANT_BLOCK; 0 = default */
+  int device;         /* CUDA device ordinal; < 0 = the calling thread's current device */
+  int use_graph;      /* 1: replay each sweep from a CUDA graph; 0: plain launches; < 0: library decides */
+} svdj_opts;
+
+typedef struct svdj_stats {
+  int sweeps;                    /* sweeps executed */
+  int converged;                 /* 1 if the last sweep rotated nothing (REL mode) */
+  int variant;                   /* variant that ran */
+  int reserved;
+  unsigned long long tested;     /* column pairs whose Gram triple was evaluated */
+  unsigned long long applied;    /* column pairs rotated */
+  unsigned long long launches;   /* kernels launched by this call */
+  double last_offdiag;           /* max over the last sweep of |a_p.a_q| / (|a_p||a_q|) */
+  double seconds_sweeps;         /* device time of the sweep loop (CUDA events) */
+  double seconds_finalize;       /* device time of sigma / U / sort */
+  double seconds_h2d;            /* host->device copies (svdj_dgesvd only) */
+  double seconds_d2h;            /* device->host copies (svdj_dgesvd only) */
+  double seconds_total;          /* wall time of the call */
+  double step_kernel_ms;         /* mean device time of the dominant sweep kernel (per launch) */
+  unsigned long long step_kernel_launches; /* launches of that kernel */
+} svdj_stats;
+
+/* Fills *opts with the defaults described above. */
+void svdj_default_opts(svdj_opts *opts);
+
+/*
+ * Host-pointer entry point: replaces the body of omp_mpi_cuda_dgesvd_local_matrices
+ * (main.cu:440-1423) and of cuda_dgesvd_kernel (main.cu:163-437).  Copies A to the device, runs the
+ * sweeps there (A and V stay resident in HBM, unlike the per-pair staging at main.cu:727-757),
+ * finalises (main.cu:1395-1411) and copies U, s, V back.  opts may be NULL (defaults); stats may be NULL.
+ */
+int svdj_dgesvd(int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, double *s, double *V,
+                size_t ldv, const svdj_opts *opts, svdj_stats *stats);
+
+/*
+ * Device-pointer entry point: same contract with A, s, V in device memory of the current (or
+ * opts->device) device; nothing crosses PCIe except the per-sweep convergence word.  `stream` is a
+ * cudaStream_t (NULL = the legacy default stream).  The reference has no device-resident
+ * counterpart (its matrices never live on the GPU: main.cu:727-757); this is the same solver minus
+ * the copies.
+ */
+int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds,
+                       double *dV, size_t ldv, const svdj_opts *opts, svdj_stats *stats, void *stream);
+
+/*
+ * One round-robin step (all n/2 disjoint pairs of step `step`, 0-based, of the reference's ordering:
+ * main.cu:526-545 for the first half, :971-990 for the second) on device buffers: Gram triple
+ * (main.cu:696-706), rotation parameters (:708-724) and the rotation of the A and V columns
+ * (jacobi_rotation, main.cu:139-147) fused in one pass.  No V initialisation, no finalisation.
+ * path: SVDJ_PATH_AUTO, or force SVDJ_PATH_REG (pair kept in registers, m <= 8192) or SVDJ_PATH_SPLIT
+ * (rows of a pair spread over several CTAs; partial Gram triples pass through d_scratch).
+ * d_scratch: device buffer of at least svdj_step_scratch_doubles(m, n) doubles; only the split path
+ * uses it; NULL makes the call allocate and free one itself.
+ * d_counters (device, 2 x unsigned long long, may be NULL): [0] += pairs rotated,
+ * [1] = max([1], bit pattern of the largest off-diagonal cosine seen).
+ * Used by the tests and by multi-GPU drivers.
+ */
+enum { SVDJ_PATH_AUTO = 0, SVDJ_PATH_REG = 1, SVDJ_PATH_SPLIT = 2 };
+int svdj_step_device(size_t m, size_t n, double *dA, size_t lda, double *dV, size_t ldv,
+                     int rotate_v, size_t step, double tol, int threshold_mode, int path,
+                     double *d_scratch, unsigned long long *d_counters, void *stream);
+
+/* Doubles of scratch the split path needs for an m x n problem. */
+size_t svdj_step_scratch_doubles(size_t m, size_t n);
+
+/* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
+size_t svdj_num_steps(size_t n);
+
+/* Host-side copy of the schedule the kernels use: writes the n/2 pairs (p,q), 0-based, of `step`
+ * into pq[0..2*(n/2)) and returns their count (main.cu:526-545, 971-990). */
+size_t svdj_schedule_step(size_t n, size_t step, size_t *pq);
+
+/* Text of the most recent error on the calling thread ("" if none). */
+const char *svdj_last_error(void);
+
+/* Library version: major*10000 + minor*100 + patch. */
+int svdj_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVDJ_H_ */

@@ -1,0 +1,435 @@
+// svdj_api.cu -- the C ABI (include/svdj.h) and the host-side sweep driver.
+//
+// Host code is C++ above a plain-C boundary, like the reference's solver functions it replaces
+// (lib/JacobiMethods.cu:191 and :1177).  The structure of a solve:
+//   V = I on the device                      (lib/JacobiMethods.cu:213-226)
+//   repeat sweeps until one rotates nothing  (the reference stops after 1: :234, :248)
+//     n-1 round-robin steps, one fused kernel launch each (:252, :697)
+//     one 16-byte read of the device counters (the reference computes :462 and drops it)
+//   sigma, sort, U = A/sigma on the device   (:1146-1164)
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <vector>
+
+#include "svdj_common.cuh"
+
+namespace svdj {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+static double now_s() {
+  using namespace std::chrono;
+  return duration<double>(steady_clock::now().time_since_epoch()).count();
+}
+
+// RAII for device / pinned buffers and events so that every early return frees them
+struct DevBuf {
+  void *p = nullptr;
+  ~DevBuf() {
+    if (p) cudaFree(p);
+  }
+  int alloc(size_t bytes) {
+    if (bytes == 0) bytes = 8;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      set_error("cudaMalloc(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
+      cudaGetLastError();
+      return SVDJ_ERR_ALLOC;
+    }
+    return SVDJ_OK;
+  }
+  template <class T>
+  T *as() const {
+    return static_cast<T *>(p);
+  }
+};
+
+struct PinBuf {
+  void *p = nullptr;
+  ~PinBuf() {
+    if (p) cudaFreeHost(p);
+  }
+  int alloc(size_t bytes) {
+    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 8);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      set_error("cudaMallocHost(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
+      cudaGetLastError();
+      return SVDJ_ERR_ALLOC;
+    }
+    return SVDJ_OK;
+  }
+  template <class T>
+  T *as() const {
+    return static_cast<T *>(p);
+  }
+};
+
+struct Event {
+  cudaEvent_t e = nullptr;
+  ~Event() {
+    if (e) cudaEventDestroy(e);
+  }
+  int create() {
+    SVDJ_CUDA_TRY(cudaEventCreate(&e));
+    return SVDJ_OK;
+  }
+};
+
+struct DeviceGuard {
+  int prev = -1;
+  bool active = false;
+  int enter(int dev) {
+    if (dev < 0) return SVDJ_OK;
+    SVDJ_CUDA_TRY(cudaGetDevice(&prev));
+    if (prev != dev) {
+      SVDJ_CUDA_TRY(cudaSetDevice(dev));
+      active = true;
+    }
+    return SVDJ_OK;
+  }
+  ~DeviceGuard() {
+    if (active) cudaSetDevice(prev);
+  }
+};
+
+static svdj_opts resolve_opts(const svdj_opts *in, size_t m) {
+  svdj_opts o;
+  svdj_default_opts(&o);
+  if (in) o = *in;
+  if (o.max_sweeps <= 0) o.max_sweeps = 60;
+  if (o.tol <= 0.0) {
+    o.tol = (o.threshold_mode == SVDJ_THRESH_ABS) ? 1e-16 : (double)(m ? m : 1) * 0x1p-53;
+  }
+  if (o.variant == SVDJ_VARIANT_AUTO) o.variant = SVDJ_VARIANT_LEVEL1;
+  return o;
+}
+
+static int check_args(int jobu, int jobv, size_t m, size_t n, const double *A, size_t lda, const double *s,
+                      const double *V, size_t ldv) {
+  if (jobu < SVDJ_ALLVEC || jobu > SVDJ_NOVEC) return -1;
+  if (jobv < SVDJ_ALLVEC || jobv > SVDJ_NOVEC) return -2;
+  if (m > 0x7fffffffu) return -3;
+  if (n > 0x7fffffffu) return -4;
+  if (A == nullptr && m * n > 0) return -5;
+  if (lda < m) return -6;
+  if (s == nullptr && std::min(m, n) > 0) return -7;
+  if (jobv != SVDJ_NOVEC) {
+    if (V == nullptr && n > 0) return -8;
+    if (ldv < n) return -9;
+  }
+  return 0;
+}
+
+// The sweep loop + finalisation on device-resident buffers.
+// vrows: rows of V the kernels rotate (n, or n rounded up to even when the buffer has a zero pad row).
+static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds,
+                           double *dV, size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st,
+                           cudaStream_t stream) {
+  const size_t mn = std::min(m, n);
+  st.variant = o.variant;
+  if (o.variant != SVDJ_VARIANT_LEVEL1) {
+    set_error("variant %d is not available in this build", o.variant);
+    return SVDJ_ERR_UNSUPPORTED;
+  }
+  if (m == 0 || n == 0) return SVDJ_OK;
+  const bool rotate_v = (jobv != SVDJ_NOVEC);
+
+  Event ev0, ev1, ev2;
+  if (int rc = ev0.create()) return rc;
+  if (int rc = ev1.create()) return rc;
+  if (int rc = ev2.create()) return rc;
+
+  DevBuf d_counters, d_scratch, d_norms, d_perm, d_tmp;
+  PinBuf h_counters, h_norms;
+  if (int rc = d_counters.alloc(sizeof(SweepCounters) * (size_t)o.max_sweeps)) return rc;
+  if (int rc = h_counters.alloc(sizeof(SweepCounters))) return rc;
+  SVDJ_CUDA_TRY(cudaMemsetAsync(d_counters.p, 0, sizeof(SweepCounters) * (size_t)o.max_sweeps, stream));
+  if (l1_uses_split(m, n)) {
+    if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
+  }
+
+  if (rotate_v) {
+    if (int rc = launch_set_identity(dV, ldv, vrows, n, stream)) return rc;
+    st.launches += 1;
+  }
+
+  const unsigned steps = (unsigned)svdj_num_steps(n);
+  const unsigned long long pairs_per_step = n / 2;
+
+  StepArgs a;
+  a.A = dA;
+  a.lda = lda;
+  a.V = dV;
+  a.ldv = ldv;
+  a.m = (unsigned)m;
+  a.n = (unsigned)n;
+  a.vrows = (unsigned)vrows;
+  a.rotate_v = rotate_v ? 1 : 0;
+  a.tol = o.tol;
+  a.threshold_mode = o.threshold_mode;
+
+  SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, stream));
+  unsigned long long step_launches = 0;
+  bool converged = false;
+  for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
+    a.counters = d_counters.as<SweepCounters>() + sweep;
+    for (unsigned k = 1; k <= steps; ++k) {
+      if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
+    }
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(h_counters.p, a.counters, sizeof(SweepCounters), cudaMemcpyDeviceToHost, stream));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+    const SweepCounters *hc = h_counters.as<SweepCounters>();
+    st.sweeps = sweep + 1;
+    st.tested += pairs_per_step * steps;
+    st.applied += hc->applied;
+    double off;
+    std::memcpy(&off, &hc->offdiag_bits, sizeof(double));
+    st.last_offdiag = off;
+    if (hc->applied == 0) {
+      converged = true;
+      break;
+    }
+  }
+  st.converged = converged ? 1 : 0;
+  st.launches += step_launches;
+  st.step_kernel_launches = step_launches;
+  SVDJ_CUDA_TRY(cudaEventRecord(ev1.e, stream));
+
+  // ---- finalisation -----------------------------------------------------------------------------
+  if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+  if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+  st.launches += 1;
+  const bool scale_u = (jobu == SVDJ_ALLVEC || jobu == SVDJ_SOMEVEC);
+
+  if (o.sort_desc) {
+    if (int rc = h_norms.alloc(sizeof(double) * n)) return rc;
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(h_norms.p, d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+    const double *nr = h_norms.as<double>();
+    std::vector<unsigned> perm(n);
+    std::iota(perm.begin(), perm.end(), 0u);
+    std::stable_sort(perm.begin(), perm.end(), [nr](unsigned x, unsigned y) { return nr[x] > nr[y]; });
+    std::vector<double> sorted(n);
+    for (size_t k2 = 0; k2 < n; ++k2) sorted[k2] = nr[perm[k2]];
+    if (int rc = d_perm.alloc(sizeof(unsigned) * n)) return rc;
+    // sorted sigma goes back into d_norms (the gather reads sigma[k] for output column k)
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(d_perm.p, perm.data(), sizeof(unsigned) * n, cudaMemcpyHostToDevice, stream));
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(d_norms.p, sorted.data(), sizeof(double) * n, cudaMemcpyHostToDevice, stream));
+    const size_t tmp_rows = std::max(m, n);
+    if (int rc = d_tmp.alloc(sizeof(double) * tmp_rows * n)) return rc;
+    // A: gather + scale into tmp, copy back
+    if (int rc = launch_gather_columns(dA, lda, d_tmp.as<double>(), m, m, n, d_perm.as<unsigned>(),
+                                       d_norms.as<double>(), scale_u ? mn : 0, stream))
+      return rc;
+    SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dA, lda * sizeof(double), d_tmp.p, m * sizeof(double), m * sizeof(double), n,
+                                    cudaMemcpyDeviceToDevice, stream));
+    st.launches += 1;
+    if (rotate_v) {
+      if (int rc = launch_gather_columns(dV, ldv, d_tmp.as<double>(), n, n, n, d_perm.as<unsigned>(), nullptr, 0,
+                                         stream))
+        return rc;
+      SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dV, ldv * sizeof(double), d_tmp.p, n * sizeof(double), n * sizeof(double), n,
+                                      cudaMemcpyDeviceToDevice, stream));
+      st.launches += 1;
+    }
+    // the host vectors must outlive the async uploads
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+  } else if (scale_u) {
+    if (int rc = launch_gather_columns(dA, lda, dA, lda, m, n, nullptr, d_norms.as<double>(), mn, stream)) return rc;
+    st.launches += 1;
+  }
+  SVDJ_CUDA_TRY(cudaMemcpyAsync(ds, d_norms.p, sizeof(double) * mn, cudaMemcpyDeviceToDevice, stream));
+  SVDJ_CUDA_TRY(cudaEventRecord(ev2.e, stream));
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+
+  float ms01 = 0.f, ms12 = 0.f;
+  SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms01, ev0.e, ev1.e));
+  SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms12, ev1.e, ev2.e));
+  st.seconds_sweeps = ms01 * 1e-3;
+  st.seconds_finalize = ms12 * 1e-3;
+  st.step_kernel_ms = step_launches ? (double)ms01 / (double)step_launches : 0.0;
+  if (o.threshold_mode == SVDJ_THRESH_REL && !converged) return SVDJ_NOT_CONVERGED;
+  return SVDJ_OK;
+}
+
+}  // namespace svdj
+
+using namespace svdj;
+
+extern "C" {
+
+void svdj_default_opts(svdj_opts *o) {
+  if (!o) return;
+  o->tol = 0.0;
+  o->max_sweeps = 60;
+  o->sort_desc = 1;
+  o->variant = SVDJ_VARIANT_AUTO;
+  o->threshold_mode = SVDJ_THRESH_REL;
+  o->block = 0;
+  o->device = -1;
+  o->use_graph = -1;
+}
+
+const char *svdj_last_error(void) { return g_error; }
+
+int svdj_version(void) { return 100; }
+
+size_t svdj_num_steps(size_t n) { return n < 2 ? 0 : 2 * ((n + 1) / 2) - 1; }
+
+size_t svdj_schedule_step(size_t n, size_t step, size_t *pq) {
+  if (n < 2 || step >= svdj_num_steps(n) || n > 0x7fffffffu) return 0;
+  const size_t pairs = n / 2;
+  for (size_t i = 0; i < pairs; ++i) {
+    Pair pr = sameh_pair((unsigned)n, (unsigned)step + 1u, (unsigned)i);
+    pq[2 * i] = pr.p;
+    pq[2 * i + 1] = pr.q;
+  }
+  return pairs;
+}
+
+size_t svdj_step_scratch_doubles(size_t m, size_t n) { return l1_scratch_doubles(m, n); }
+
+int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
+                       size_t ldv, const svdj_opts *opts, svdj_stats *stats, void *stream) {
+  g_error[0] = 0;
+  svdj_stats local;
+  svdj_stats &st = stats ? *stats : local;
+  std::memset(&st, 0, sizeof(st));
+  if (int bad = check_args(jobu, jobv, m, n, dA, lda, ds, dV, ldv)) {
+    set_error("svdj_dgesvd_device: argument %d is invalid", -bad);
+    return bad;
+  }
+  const double t0 = now_s();
+  svdj_opts o = resolve_opts(opts, m);
+  DeviceGuard guard;
+  if (int rc = guard.enter(o.device)) return rc;
+  int rc = solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, n, o, st, static_cast<cudaStream_t>(stream));
+  st.seconds_total = now_s() - t0;
+  return rc;
+}
+
+int svdj_dgesvd(int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, double *s, double *V, size_t ldv,
+                const svdj_opts *opts, svdj_stats *stats) {
+  g_error[0] = 0;
+  svdj_stats local;
+  svdj_stats &st = stats ? *stats : local;
+  std::memset(&st, 0, sizeof(st));
+  if (int bad = check_args(jobu, jobv, m, n, A, lda, s, V, ldv)) {
+    set_error("svdj_dgesvd: argument %d is invalid", -bad);
+    return bad;
+  }
+  const double t0 = now_s();
+  svdj_opts o = resolve_opts(opts, m);
+  DeviceGuard guard;
+  if (int rc = guard.enter(o.device)) return rc;
+  const size_t mn = std::min(m, n);
+  if (m == 0 || n == 0) return SVDJ_OK;
+
+  // Device copies are padded to an even number of rows (a zero row changes neither the Gram triples
+  // nor the rotations) and to 128-byte columns, so that the vectorised kernels always apply.
+  const bool want_v = (jobv != SVDJ_NOVEC);
+  const size_t m_pad = (m + 1) & ~size_t(1);
+  const size_t n_pad = (n + 1) & ~size_t(1);
+  const size_t lda_d = (m_pad + 15) & ~size_t(15);
+  const size_t ldv_d = (n_pad + 15) & ~size_t(15);
+  const size_t n_cols = n;
+
+  cudaStream_t stream = nullptr;
+  SVDJ_CUDA_TRY(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  struct StreamGuard {
+    cudaStream_t s;
+    ~StreamGuard() { cudaStreamDestroy(s); }
+  } sguard{stream};
+
+  DevBuf dA, dV, ds;
+  if (int rc = dA.alloc(sizeof(double) * lda_d * n_cols)) return rc;
+  if (int rc = ds.alloc(sizeof(double) * std::max<size_t>(mn, 1))) return rc;
+  if (want_v) {
+    if (int rc = dV.alloc(sizeof(double) * ldv_d * n_cols)) return rc;
+  }
+
+  double t = now_s();
+  if (m_pad != m) SVDJ_CUDA_TRY(cudaMemsetAsync(dA.p, 0, sizeof(double) * lda_d * n_cols, stream));
+  SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dA.p, lda_d * sizeof(double), A, lda * sizeof(double), m * sizeof(double), n,
+                                  cudaMemcpyHostToDevice, stream));
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+  st.seconds_h2d = now_s() - t;
+
+  // V is n x n; with n odd the kernels see n_pad rows (the identity init writes the pad row as zero)
+  int rc = solve_on_device(jobu, jobv, m_pad, n, dA.as<double>(), lda_d, ds.as<double>(), dV.as<double>(), ldv_d,
+                           n_pad, o, st, stream);
+  if (rc != SVDJ_OK && rc != SVDJ_NOT_CONVERGED) return rc;
+
+  t = now_s();
+  SVDJ_CUDA_TRY(cudaMemcpy2DAsync(A, lda * sizeof(double), dA.p, lda_d * sizeof(double), m * sizeof(double), n,
+                                  cudaMemcpyDeviceToHost, stream));
+  SVDJ_CUDA_TRY(cudaMemcpyAsync(s, ds.p, sizeof(double) * mn, cudaMemcpyDeviceToHost, stream));
+  if (want_v) {
+    SVDJ_CUDA_TRY(cudaMemcpy2DAsync(V, ldv * sizeof(double), dV.p, ldv_d * sizeof(double), n * sizeof(double), n,
+                                    cudaMemcpyDeviceToHost, stream));
+  }
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+  st.seconds_d2h = now_s() - t;
+  st.seconds_total = now_s() - t0;
+  return rc;
+}
+
+int svdj_step_device(size_t m, size_t n, double *dA, size_t lda, double *dV, size_t ldv, int rotate_v, size_t step,
+                     double tol, int threshold_mode, int path, double *d_scratch, unsigned long long *d_counters,
+                     void *stream) {
+  g_error[0] = 0;
+  if (m == 0 || m > 0x7fffffffu) return -1;
+  if (n > 0x7fffffffu) return -2;
+  if (dA == nullptr) return -3;
+  if (lda < m) return -4;
+  if (rotate_v && dV == nullptr) return -5;
+  if (rotate_v && ldv < n) return -6;
+  if (step >= svdj_num_steps(n)) return -8;
+  if (path < SVDJ_PATH_AUTO || path > SVDJ_PATH_SPLIT) return -11;
+  StepArgs a;
+  a.A = dA;
+  a.lda = lda;
+  a.V = dV;
+  a.ldv = ldv;
+  a.m = (unsigned)m;
+  a.n = (unsigned)n;
+  a.vrows = (unsigned)n;
+  a.rotate_v = rotate_v ? 1 : 0;
+  a.tol = tol;
+  a.threshold_mode = threshold_mode;
+  a.counters = reinterpret_cast<SweepCounters *>(d_counters);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned k = (unsigned)step + 1u;
+  const bool split = (path == SVDJ_PATH_SPLIT) || (path == SVDJ_PATH_AUTO && l1_uses_split(m, n));
+  if (!split) {
+    if (l1_uses_split(m, n)) {
+      set_error("svdj_step_device: the register path holds at most 8192 rows (m = %zu)", m);
+      return SVDJ_ERR_UNSUPPORTED;
+    }
+    return l1_launch_step(a, k, nullptr, st, nullptr);
+  }
+  DevBuf own;
+  if (d_scratch == nullptr) {
+    if (int rc = own.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
+    d_scratch = own.as<double>();
+  }
+  int rc = l1_launch_split(a, k, d_scratch, st, nullptr);
+  if (own.p) SVDJ_CUDA_TRY(cudaStreamSynchronize(st));  // the scratch is freed on return
+  return rc;
+}
+
+}  // extern "C"

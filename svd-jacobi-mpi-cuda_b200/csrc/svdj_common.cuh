@@ -1,0 +1,171 @@
+// svdj_common.cuh -- shared device/host helpers of libsvdj (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/svdj.h"
+
+namespace svdj {
+
+// ---------------------------------------------------------------------------------------------
+// error plumbing: every CUDA call is checked (the reference checks none)
+// ---------------------------------------------------------------------------------------------
+void set_error(const char *fmt, ...);
+
+#define SVDJ_CUDA_TRY(expr)                                                                   \
+  do {                                                                                        \
+    cudaError_t e__ = (expr);                                                                 \
+    if (e__ != cudaSuccess) {                                                                 \
+      ::svdj::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
+      return SVDJ_ERR_CUDA;                                                                   \
+    }                                                                                         \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// per-sweep counters kept on the device (what lib/JacobiMethods.cu:462 computes and drops)
+// ---------------------------------------------------------------------------------------------
+struct SweepCounters {
+  unsigned long long applied;       // pairs rotated
+  unsigned long long offdiag_bits;  // bit pattern of max |alpha|/sqrt(beta*gamma); non-negative doubles order like uint64
+};
+
+// ---------------------------------------------------------------------------------------------
+// The reference's round-robin ordering (lib/JacobiMethods.cu:250-251 attributes it to Sameh 1971).
+// Step k = 1 .. 2*m_ord-1 with m_ord = (n+1)/2; every step holds n/2 disjoint pairs, indexed here by
+// idx = 0 .. n/2-1 in the order of the reference's q loop.  Columns are 1-based inside, 0-based out.
+// Restates lib/JacobiMethods.cu:278-290 (k < m_ord) and :723-735 (k >= m_ord).
+// ---------------------------------------------------------------------------------------------
+struct Pair {
+  unsigned p, q;
+};
+
+__host__ __device__ inline Pair sameh_pair(unsigned n, unsigned k, unsigned idx) {
+  const unsigned h = (n + 1u) >> 1;  // m_ordering
+  unsigned q, p;
+  if (k < h) {
+    q = h - k + 1u + idx;  // q runs h-k+1 .. n-k
+    if (q <= 2u * h - 2u * k) {
+      p = 2u * h - 2u * k + 1u - q;
+    } else if (q <= 2u * h - k - 1u) {
+      p = 4u * h - 2u * k - q;
+    } else {
+      p = n;
+    }
+  } else {
+    q = 4u * h - n - k + idx;  // q runs 4h-n-k .. 3h-k-1
+    if (q < 2u * h - k + 1u) {
+      p = n;
+    } else if (q <= 4u * h - 2u * k - 1u) {
+      p = 4u * h - 2u * k - q;
+    } else {
+      p = 6u * h - 2u * k - 1u - q;
+    }
+  }
+  Pair r;
+  r.p = p - 1u;
+  r.q = q - 1u;
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Rotation parameters from the Gram triple; restates lib/JacobiMethods.cu:464-477.
+// alpha = a_p.a_q, beta = |a_p|^2, gamma = |a_q|^2.  Returns false when the pair is left alone.
+// ---------------------------------------------------------------------------------------------
+struct Rot {
+  double c, s;
+};
+
+__host__ __device__ inline bool rotation_from_gram(double alpha, double beta, double gamma, double tol,
+                                                   int threshold_mode, Rot &r, double &offdiag) {
+  const double denom = sqrt(beta * gamma);
+  offdiag = denom > 0.0 ? fabs(alpha) / denom : 0.0;
+  const bool rotate = (threshold_mode == SVDJ_THRESH_ABS) ? (fabs(alpha) > tol) : (fabs(alpha) > tol * denom);
+  if (!rotate) {
+    r.c = 1.0;
+    r.s = 0.0;
+    return false;
+  }
+  const double tau = (gamma - beta) / (2.0 * alpha);
+  const double root = sqrt(1.0 + tau * tau);
+  const double t = 1.0 / (tau >= 0.0 ? tau + root : tau - root);
+  r.c = 1.0 / sqrt(1.0 + t * t);
+  r.s = t * r.c;
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// warp / block reductions
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sum of three values over the block.  Every thread returns the same bits (xor-butterfly in the warp,
+// then each thread adds the per-warp partials in the same order), so every thread derives the same (c,s).
+template <int THREADS>
+__device__ __forceinline__ void block_sum3(double &a, double &b, double &c, double *smem /* 3*THREADS/32 */) {
+  constexpr int WARPS = THREADS / 32;
+  a = warp_sum(a);
+  b = warp_sum(b);
+  c = warp_sum(c);
+  if (WARPS == 1) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    smem[warp] = a;
+    smem[WARPS + warp] = b;
+    smem[2 * WARPS + warp] = c;
+  }
+  __syncthreads();
+  double sa = 0.0, sb = 0.0, sc = 0.0;
+#pragma unroll
+  for (int w = 0; w < WARPS; ++w) {
+    sa += smem[w];
+    sb += smem[WARPS + w];
+    sc += smem[2 * WARPS + w];
+  }
+  a = sa;
+  b = sb;
+  c = sc;
+}
+
+__device__ __forceinline__ void publish_pair(SweepCounters *ctr, bool rotated, double offdiag) {
+  if (ctr == nullptr) return;
+  if (rotated) atomicAdd(&ctr->applied, 1ull);
+  atomicMax(&ctr->offdiag_bits, (unsigned long long)__double_as_longlong(offdiag));
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers implemented in the .cu files
+// ---------------------------------------------------------------------------------------------
+struct StepArgs {
+  double *A;
+  size_t lda;
+  double *V;
+  size_t ldv;
+  unsigned m, n;
+  unsigned vrows;  // rows of V to rotate: n, or n padded with zero rows
+  int rotate_v;
+  double tol;
+  int threshold_mode;
+  SweepCounters *counters;  // may be null
+};
+
+// Level-1 fused step (svdj_l1.cu).  k = 1-based step of the reference ordering.
+// scratch: device buffer of l1_scratch_doubles(m, n) doubles, only needed when l1_uses_split(m, n).
+int l1_launch_step(const StepArgs &a, unsigned k, double *scratch, cudaStream_t st, unsigned long long *launches);
+int l1_launch_split(const StepArgs &a, unsigned k, double *scratch, cudaStream_t st, unsigned long long *launches);
+bool l1_uses_split(size_t m, size_t n);
+size_t l1_scratch_doubles(size_t m, size_t n);
+
+// Finalisation (svdj_finalize.cu)
+int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st);
+int launch_column_norms(const double *A, size_t lda, size_t m, size_t n, double *norms, cudaStream_t st);
+// out[:, k] = in[:, perm[k]] * (scale ? 1/sigma[k] : 1); columns k >= ncols_scaled copied unscaled
+int launch_gather_columns(const double *in, size_t ldin, double *out, size_t ldout, size_t rows, size_t ncols,
+                          const unsigned *perm, const double *sigma, size_t ncols_scaled, cudaStream_t st);
+
+}  // namespace svdj
