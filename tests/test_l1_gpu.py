@@ -3,7 +3,7 @@
 Tolerances (BASELINE.json north_star): sorted sigma to <= 1e-12 (normwise: max|ds_i| / s_max, the only
 meaningful reading once cond*eps approaches 1e-12), U and V up to column sign, ||U^T U - I||_max,
 ||V^T V - I||_max and ||A - U S V^T||_F / ||A||_F <= 10 * max(m,n) * eps with eps = 2^-52.
-Single steps are compared with the oracle's fma-rotating mode to 64 ulp-ish (1e-13 relative to the
+Single steps are compared with the oracle's fma-rotating mode to 64*m*2^-53 (relative to the
 column scale): the device sums the Gram triple in a different order than the host loop.
 """
 import glob
@@ -49,9 +49,10 @@ def test_single_steps_match_oracle(svdj, m, n, path):
                          path=svdj.PATH_REG if path == "reg" else svdj.PATH_SPLIT, d_counters=ctr.data_ptr())
     torch.cuda.synchronize()
     gA, gV = _host(dA, m, n), _host(dV, n, n)
-    scale = np.abs(A0).max() * np.sqrt(m)
-    assert np.abs(gA - A).max() <= 1e-13 * scale
-    assert np.abs(gV - V).max() <= 1e-13
+    # the Gram triple is summed in a different order on the device, so (c,s) differ by ~m*eps relative
+    tol_cmp = 64 * m * 2.0 ** -53
+    assert np.abs(gA - A).max() <= tol_cmp * np.abs(A0).max() * np.sqrt(m)
+    assert np.abs(gV - V).max() <= tol_cmp
     assert int(ctr[0].item()) == applied
     off = np.array([ctr[1].item()], dtype=np.int64).view(np.float64)[0]
     assert 0.0 <= off <= 1.0 + 1e-12
