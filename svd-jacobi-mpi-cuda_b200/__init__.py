@@ -183,13 +183,13 @@ def dgesvd(jobu, jobv, m, n, A, lda, s, V, ldv, opts: Opts | None = None, allow_
 # exactly one sweep, absolute threshold, no sorting.
 def cuda_dgesvd_kernel(jobu, jobv, m, n, A, lda, s, V, ldv, reference_mode=False, **optkw) -> Stats:
     if reference_mode:
-        optkw = dict(max_sweeps=1, threshold_mode=THRESH_ABS, tol=1e-20, sort_desc=0, **optkw)
+        optkw = {**dict(max_sweeps=1, threshold_mode=THRESH_ABS, tol=1e-20, sort_desc=0), **optkw}
     return dgesvd(jobu, jobv, m, n, A, lda, s, V, ldv, default_opts(**optkw), allow_not_converged=reference_mode)
 
 
 def omp_mpi_cuda_dgesvd_local_matrices(jobu, jobv, m, n, A, lda, s, V, ldv, reference_mode=False, **optkw) -> Stats:
     if reference_mode:
-        optkw = dict(max_sweeps=1, threshold_mode=THRESH_ABS, tol=1e-16, sort_desc=0, **optkw)
+        optkw = {**dict(max_sweeps=1, threshold_mode=THRESH_ABS, tol=1e-16, sort_desc=0), **optkw}
     return dgesvd(jobu, jobv, m, n, A, lda, s, V, ldv, default_opts(**optkw), allow_not_converged=reference_mode)
 
 
