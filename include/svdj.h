@@ -130,6 +130,30 @@ int svdj_step_device(size_t m, size_t n, double *dA, size_t lda, double *dV, siz
 /* Doubles of scratch the split path needs for an m x n problem. */
 size_t svdj_step_scratch_doubles(size_t m, size_t n);
 
+/*
+ * The same round-robin step as svdj_step_device(path = SVDJ_PATH_SPLIT), for callers that must not
+ * allocate device memory.  It has no counterpart in the reference (which allocates per call,
+ * main.cu:484-494); it exists for the callers of THIS library who cannot call cudaMalloc: drivers that
+ * keep several streams busy and would have all of them stalled by the device-wide synchronisation
+ * inside cudaMalloc/cudaFree, processes whose device memory was handed to a single arena at start-up so
+ * that the driver has nothing left to give, and callers with a fixed latency budget per step.
+ * The partial Gram triples go through an array that is part of the library image on every GPU that
+ * loads libsvdj.so (SVDJ_NOALLOC_MAX_SCRATCH_DOUBLES doubles = 768 KiB, held until the process exits).
+ * The call makes no cudaMalloc/cudaFree and no other allocating call.
+ *   - Problems with svdj_step_scratch_doubles(m, n) > SVDJ_NOALLOC_MAX_SCRATCH_DOUBLES are refused
+ *     with SVDJ_ERR_UNSUPPORTED and a message in svdj_last_error().
+ *   - Every call on a GPU uses the same array: calls whose kernels may overlap on that GPU (two streams,
+ *     two threads) race.  The array keeps the previous call's contents; the step overwrites every cell
+ *     it later reads, so nothing has to be cleared.
+ *   - The first call on each GPU (made with that GPU current) resolves the array's device address and
+ *     caches it; make that first call before any stream capture starts.
+ * A, V, counters and stream are as for svdj_step_device.
+ */
+#define SVDJ_NOALLOC_MAX_SCRATCH_DOUBLES 98304
+int svdj_step_device_noalloc(size_t m, size_t n, double *dA, size_t lda, double *dV, size_t ldv,
+                             int rotate_v, size_t step, double tol, int threshold_mode,
+                             unsigned long long *d_counters, void *stream);
+
 /* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
 size_t svdj_num_steps(size_t n);
 

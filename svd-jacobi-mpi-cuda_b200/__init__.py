@@ -77,6 +77,7 @@ EXPORTS = (
     "svdj_dgesvd_device",
     "svdj_step_device",
     "svdj_step_scratch_doubles",
+    "svdj_step_device_noalloc",
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_last_error",
@@ -100,6 +101,8 @@ def _load() -> C.CDLL:
     lib.svdj_dgesvd_device.restype = i
     lib.svdj_step_device.argtypes = [sz, sz, vp, sz, vp, sz, i, sz, dbl, i, i, vp, vp, vp]
     lib.svdj_step_device.restype = i
+    lib.svdj_step_device_noalloc.argtypes = [sz, sz, vp, sz, vp, sz, i, sz, dbl, i, vp, vp]
+    lib.svdj_step_device_noalloc.restype = i
     lib.svdj_step_scratch_doubles.argtypes = [sz, sz]
     lib.svdj_step_scratch_doubles.restype = sz
     lib.svdj_num_steps.argtypes = [sz]
@@ -215,3 +218,15 @@ def step_device(m, n, dA: int, lda, dV: int, ldv, rotate_v, step, tol, threshold
 
 def step_scratch_doubles(m: int, n: int) -> int:
     return int(lib.svdj_step_scratch_doubles(m, n))
+
+
+NOALLOC_MAX_SCRATCH_DOUBLES = 98304  # SVDJ_NOALLOC_MAX_SCRATCH_DOUBLES in include/svdj.h
+
+
+def step_device_noalloc(m, n, dA: int, lda, dV: int, ldv, rotate_v, step, tol, threshold_mode=THRESH_REL,
+                        d_counters: int = 0, stream: int = 0) -> None:
+    """Split-path step whose scratch is the array built into libsvdj.so: for callers that cannot
+    allocate device memory (see include/svdj.h).  Calls that may overlap on one GPU race on that array."""
+    rc = lib.svdj_step_device_noalloc(m, n, dA, lda, dV or None, ldv, int(rotate_v), step, tol, threshold_mode,
+                                      d_counters or None, stream or None)
+    _check(rc)
