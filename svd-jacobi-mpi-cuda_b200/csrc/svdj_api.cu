@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <vector>
@@ -114,7 +115,6 @@ static svdj_opts resolve_opts(const svdj_opts *in, size_t m) {
   if (o.tol <= 0.0) {
     o.tol = (o.threshold_mode == SVDJ_THRESH_ABS) ? 1e-16 : (double)(m ? m : 1) * 0x1p-53;
   }
-  if (o.variant == SVDJ_VARIANT_AUTO) o.variant = SVDJ_VARIANT_LEVEL1;
   return o;
 }
 
@@ -140,11 +140,20 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
                            double *dV, size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st,
                            cudaStream_t stream) {
   const size_t mn = std::min(m, n);
-  st.variant = o.variant;
-  if (o.variant != SVDJ_VARIANT_LEVEL1) {
-    set_error("variant %d is not available in this build", o.variant);
+  int variant = o.variant;
+  if (variant == SVDJ_VARIANT_AUTO) {
+    // block Jacobi moves ~13x fewer bytes per sweep; it needs a few block pairs per step to fill the GPU
+    variant = (blk_num_blocks(n) >= 4 && o.threshold_mode == SVDJ_THRESH_REL) ? SVDJ_VARIANT_BLOCK : SVDJ_VARIANT_LEVEL1;
+  }
+  if (variant != SVDJ_VARIANT_LEVEL1 && variant != SVDJ_VARIANT_BLOCK) {
+    set_error("unknown variant %d", variant);
     return SVDJ_ERR_UNSUPPORTED;
   }
+  if (variant == SVDJ_VARIANT_BLOCK && (blk_num_blocks(n) < 2 || o.threshold_mode != SVDJ_THRESH_REL)) {
+    variant = SVDJ_VARIANT_LEVEL1;  // a single block has no partner; the absolute test is the reference's level-1 rule
+  }
+  st.variant = variant;
+  const bool block = (variant == SVDJ_VARIANT_BLOCK);
   if (m == 0 || n == 0) return SVDJ_OK;
   const bool rotate_v = (jobv != SVDJ_NOVEC);
 
@@ -158,7 +167,14 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (int rc = d_counters.alloc(sizeof(SweepCounters) * (size_t)o.max_sweeps)) return rc;
   if (int rc = h_counters.alloc(sizeof(SweepCounters))) return rc;
   SVDJ_CUDA_TRY(cudaMemsetAsync(d_counters.p, 0, sizeof(SweepCounters) * (size_t)o.max_sweeps, stream));
-  if (l1_uses_split(m, n)) {
+  DevBuf d_gpart, d_w, d_wflag;
+  if (block) {
+    size_t gp = 0, wd = 0, fl = 0;
+    blk_scratch_sizes(m, n, &gp, &wd, &fl);
+    if (int rc = d_gpart.alloc(sizeof(double) * gp)) return rc;
+    if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
+    if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
+  } else if (l1_uses_split(m, n)) {
     if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
   }
 
@@ -167,8 +183,30 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     st.launches += 1;
   }
 
-  const unsigned steps = (unsigned)svdj_num_steps(n);
-  const unsigned long long pairs_per_step = n / 2;
+  const unsigned nb = blk_num_blocks(n);
+  const unsigned steps = (unsigned)svdj_num_steps(block ? nb : n);
+  // column pairs looked at per step: n/2 on the level-1 path, 496 per block pair on the block path
+  const unsigned long long pairs_per_step = block ? (unsigned long long)(nb / 2) * 496ull : n / 2;
+
+  BlockArgs b;
+  b.A = dA;
+  b.lda = lda;
+  b.V = dV;
+  b.ldv = ldv;
+  b.m = (unsigned)m;
+  b.n = (unsigned)n;
+  b.vrows = (unsigned)vrows;
+  b.rotate_v = rotate_v ? 1 : 0;
+  b.nb = nb;
+  b.tol = o.tol;
+  b.threshold_mode = o.threshold_mode;
+  // Two cyclic sweeps of the 32 x 32 eigen-solve per visit: measured to need as few outer sweeps as a fully
+  // converged inner solve, at a third of its latency.  SVDJ_INNER_SWEEPS overrides.
+  b.max_inner_sweeps = 2;
+  if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) {
+    const int v = std::atoi(env);
+    if (v > 0) b.max_inner_sweeps = v;
+  }
 
   StepArgs a;
   a.A = dA;
@@ -187,8 +225,15 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   bool converged = false;
   for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
     a.counters = d_counters.as<SweepCounters>() + sweep;
+    b.counters = a.counters;
     for (unsigned k = 1; k <= steps; ++k) {
-      if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
+      if (block) {
+        if (int rc = blk_launch_step(b, k, d_gpart.as<double>(), d_w.as<double>(), d_wflag.as<int>(), stream,
+                                     &step_launches))
+          return rc;
+      } else {
+        if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
+      }
     }
     SVDJ_CUDA_TRY(cudaMemcpyAsync(h_counters.p, a.counters, sizeof(SweepCounters), cudaMemcpyDeviceToHost, stream));
     SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));

@@ -1,0 +1,427 @@
+// svdj_block.cu -- block one-sided Jacobi step: the same orthogonalisation as the level-1 path, done
+// for 2b = 32 columns at a time so that the work becomes dense FP64 contractions.
+//
+// A round-robin step of the reference rotates n/2 column pairs, each from its own Gram triple
+// (lib/JacobiMethods.cu:450-510).  Here a step takes nb/2 disjoint pairs of column BLOCKS (b = 16
+// columns each, blocks paired by the same round-robin ordering, lib/JacobiMethods.cu:278-290) and for
+// every block pair X = [A_I A_J] (m x 32), Y = [V_I V_J] (n x 32):
+//   K1 blk_gram_kernel    G = X^T X            FP64 tensor-core tiles (mma.sync m8n8k4 = DMMA), HBM/tensor ridge
+//   K2 blk_eig_kernel     G = W L W^T          cyclic two-sided Jacobi on the 32 x 32 Gram matrix in shared
+//                                              memory: the reference's rotation formulas (:464-477) applied to
+//                                              Gram entries instead of freshly summed dot products
+//   K3 blk_update_kernel  X <- X W, Y <- Y W   FP64 tensor-core tiles, HBM-bound
+// One block pair covers b(2b-1) = 496 column pairs for 16b(3m+2n) bytes of traffic, against 32(m+n) per
+// pair on the level-1 path: ~0.8 b = 13x fewer bytes per sweep; flops rise to 10 n^3 per sweep (m = n).
+// tcgen05 has no FP64 kind, so mma.sync DMMA is the sm_100a FP64 tensor path (profiles/r1_fp64_peaks.md).
+#include "svdj_common.cuh"
+
+namespace svdj {
+
+static constexpr int kBW = 16;                 // block width b
+static constexpr int kD = 2 * kBW;             // columns of a block pair
+static constexpr int kGramTiles = 10;          // upper triangle of the 4 x 4 grid of 8 x 8 tiles
+static constexpr int kGramPart = kGramTiles * 64;
+static constexpr unsigned kNoCol = 0xffffffffu;
+
+__device__ __forceinline__ void dmma884(double &d0, double &d1, const double a, const double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
+// Global column held by slot s (0..31) of block pair (I, J); kNoCol past the last column (ragged last block:
+// such a slot behaves as a zero column and is never written).
+__device__ __forceinline__ unsigned slot_col(unsigned I, unsigned J, unsigned s, unsigned n) {
+  const unsigned c = (s < kBW) ? I * kBW + s : J * kBW + (s - kBW);
+  return c < n ? c : kNoCol;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: partial Gram matrices.  grid (block pairs, row splits); each warp walks 4-row k-steps of its
+// rows.  For G = X^T X the A fragment of tile row ti and the B fragment of tile column tj are the same
+// 32 numbers X[k0 + lane%4][8t + lane/4], so 4 loads feed the 10 DMMAs of a k-step.
+// gpart layout: [pair][split][tile t][lane][e], tile t = (ti<=tj) in row-major order of the upper triangle.
+// ------------------------------------------------------------------------------------------------
+template <int WARPS, int UNROLL>
+__global__ void __launch_bounds__(WARPS * 32) blk_gram_kernel(const BlockArgs a, const unsigned k,
+                                                              const unsigned rows_per_split,
+                                                              double *__restrict__ gpart) {
+  __shared__ double red[WARPS][kGramPart];
+  const Pair bp = sameh_pair(a.nb, k, blockIdx.x);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+  const double *cp[4];
+  bool cv[4];
+#pragma unroll
+  for (int gi = 0; gi < 4; ++gi) {
+    const unsigned c = slot_col(bp.p, bp.q, 8 * gi + g, a.n);
+    cv[gi] = (c != kNoCol);
+    cp[gi] = a.A + (size_t)(cv[gi] ? c : 0) * a.lda;
+  }
+  const unsigned r0 = blockIdx.y * rows_per_split;
+  const unsigned r1 = min(a.m, r0 + rows_per_split);
+  double acc[kGramTiles][2];
+#pragma unroll
+  for (int t = 0; t < kGramTiles; ++t) acc[t][0] = acc[t][1] = 0.0;
+
+  for (unsigned kr = r0 + 4 * warp; kr < r1; kr += 4 * WARPS * UNROLL) {
+    double f[UNROLL][4];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const unsigned row = kr + 4 * WARPS * u + tg;
+#pragma unroll
+      for (int gi = 0; gi < 4; ++gi) f[u][gi] = (cv[gi] && row < r1) ? cp[gi][row] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      int t = 0;
+#pragma unroll
+      for (int ti = 0; ti < 4; ++ti)
+#pragma unroll
+        for (int tj = ti; tj < 4; ++tj) {
+          dmma884(acc[t][0], acc[t][1], f[u][ti], f[u][tj]);
+          ++t;
+        }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < kGramTiles; ++t) {
+    red[warp][t * 64 + lane * 2 + 0] = acc[t][0];
+    red[warp][t * 64 + lane * 2 + 1] = acc[t][1];
+  }
+  __syncthreads();
+  double *dst = gpart + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * kGramPart;
+  for (unsigned i = threadIdx.x; i < kGramPart; i += WARPS * 32) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) s += red[w][i];
+    dst[i] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: eigen-decomposition of the 32 x 32 Gram matrix by cyclic two-sided Jacobi, all in shared memory.
+// One CTA of 256 threads per block pair.  A parallel step holds 16 disjoint index pairs (circle
+// method).  Every warp computes the step's 16 rotations itself (lanes j and j+16 both do pair j), so no
+// broadcast through shared memory is needed; thread (j1, j2) owns the 2 x 2 block G[{p1,q1}][{p2,q2}]
+// and applies J1^T . J2 to it, reading the old matrix and writing the other buffer: one barrier per
+// step.  W accumulates the rotations, is pulled back to orthogonality to O(eps) by one Newton-Schulz
+// step (otherwise the defect of thousands of products adds up linearly in V), and its columns are
+// ordered by decreasing eigenvalue, which keeps the larger columns in the first block of the pair
+// (de Rijk's ordering at block level: ~25 % fewer outer sweeps).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void circle_pair(int t, int j, int &p, int &q) {
+  // 31 rounds over 32 players: player 31 stays, the others rotate
+  int x, y;
+  if (j == 0) {
+    x = t;
+    y = kD - 1;
+  } else {
+    x = t + j;
+    x = x >= kD - 1 ? x - (kD - 1) : x;
+    y = t - j;
+    y = y < 0 ? y + (kD - 1) : y;
+  }
+  p = min(x, y);
+  q = max(x, y);
+}
+
+// Same rotation as lib/JacobiMethods.cu:464-477 (tau, t = sgn(tau)/(|tau|+sqrt(1+tau^2)), c = 1/sqrt(1+t^2),
+// s = t c), evaluated without divisions through cos(2 theta) = |zeta| / h, zeta = gamma - beta, h = hypot(zeta, 2 alpha):
+//   c = sqrt((1 + |zeta|/h) / 2),  s = sgn(zeta) * alpha / (h c).
+// Two rsqrt instead of three divisions and two square roots on the critical path of every step.
+__device__ __forceinline__ void fast_rotation(double alpha, double beta, double gamma, double &c, double &s) {
+  const double zeta = gamma - beta;
+  const double a2 = 2.0 * alpha;
+  // scale to avoid under/overflow of the squares (Gram entries span the square of the column norms' range)
+  const double big = fmax(fabs(zeta), fabs(a2));
+  const int e = ilogb(big);
+  const double z = scalbn(zeta, -e), y = scalbn(a2, -e);
+  const double rh = rsqrt(z * z + y * y);
+  const double cc = 0.5 + 0.5 * fabs(z) * rh;
+  const double rcc = rsqrt(cc);
+  c = cc * rcc;
+  s = (zeta >= 0.0 ? 0.5 : -0.5) * y * rh * rcc;
+}
+
+__global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
+                                                      const double *__restrict__ gpart, double *__restrict__ wbuf,
+                                                      int *__restrict__ wflag) {
+  __shared__ double Gb[2][kD][kD + 1];
+  __shared__ double W[kD][kD + 1];
+  __shared__ double T[kD][kD + 1];
+  __shared__ unsigned long long fresh_max;
+  __shared__ int rank_of[kD];
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  const unsigned pair = blockIdx.x;
+
+  // sum the partial Gram matrices in a fixed order (deterministic) and unpack the DMMA tile layout
+  const double *src = gpart + (size_t)pair * splits * kGramPart;
+  for (unsigned i = tid; i < kGramPart; i += 256) {
+    double s = 0.0;
+    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart + i];
+    const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
+    int ti = 0, rem = t;  // t -> (ti, tj) of the upper triangle: rows of 4, 3, 2, 1 tiles
+    while (rem >= 4 - ti) {
+      rem -= 4 - ti;
+      ++ti;
+    }
+    const int tj = ti + rem;
+    const int r = 8 * ti + (l >> 2), c = 8 * tj + 2 * (l & 3) + e;
+    Gb[0][r][c] = s;
+    if (ti != tj) Gb[0][c][r] = s;
+  }
+  for (unsigned i = tid; i < kD * kD; i += 256) W[i >> 5][i & 31] = ((i >> 5) == (i & 31)) ? 1.0 : 0.0;
+  if (tid == 0) fresh_max = 0ull;
+  __syncthreads();
+
+  // largest off-diagonal cosine of the fresh Gram matrix (what lib/JacobiMethods.cu:462 computes per pair)
+  {
+    double mx = 0.0;
+    for (unsigned i = tid; i < kD * kD; i += 256) {
+      const int r = i >> 5, c = i & 31;
+      if (r < c) {
+        const double den = sqrt(Gb[0][r][r] * Gb[0][c][c]);
+        const double off = den > 0.0 ? fabs(Gb[0][r][c]) / den : 0.0;
+        mx = fmax(mx, off);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(mx));
+  }
+
+  int total_rot = 0;
+  int cur = 0;
+  const int j1 = tid >> 4, j2 = tid & 15;
+  const double tol2 = a.tol * a.tol;
+  for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+    int sweep_rot = 0;
+    for (int t = 0; t < kD - 1; ++t) {
+      // the step's 16 rotations, computed by every warp (lane & 15 = pair index)
+      int p2, q2;
+      circle_pair(t, j2, p2, q2);
+      const double al = Gb[cur][p2][q2], be = Gb[cur][p2][p2], ga = Gb[cur][q2][q2];
+      const bool rot = al * al > tol2 * be * ga;  // |alpha| > tol sqrt(beta gamma), lib/JacobiMethods.cu:462/466
+      double c2 = 1.0, s2 = 0.0;
+      if (rot) fast_rotation(al, be, ga, c2, s2);
+      const unsigned mask = __ballot_sync(0xffffffffu, rot) & 0xffffu;
+      if (mask == 0u) continue;  // every warp sees the same 16 decisions: uniform across the CTA
+      sweep_rot += __popc(mask);
+      const int p1 = __shfl_sync(0xffffffffu, p2, j1), q1 = __shfl_sync(0xffffffffu, q2, j1);
+      const double c1 = __shfl_sync(0xffffffffu, c2, j1), s1 = __shfl_sync(0xffffffffu, s2, j1);
+      {
+        const double g11 = Gb[cur][p1][p2], g12 = Gb[cur][p1][q2], g21 = Gb[cur][q1][p2], g22 = Gb[cur][q1][q2];
+        // columns: col_p' = c col_p - s col_q, col_q' = s col_p + c col_q (the kernel at :1483-1491)
+        const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
+        const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
+        // rows: the transpose of the same rotation
+        double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
+        double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
+        if (j1 == j2 && s1 != 0.0) {
+          n12 = 0.0;  // the rotated pair is orthogonal by construction
+          n21 = 0.0;
+        }
+        Gb[cur ^ 1][p1][p2] = n11;
+        Gb[cur ^ 1][p1][q2] = n12;
+        Gb[cur ^ 1][q1][p2] = n21;
+        Gb[cur ^ 1][q1][q2] = n22;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int r = j1 + 16 * i;  // rows r of W, pair j2
+          const double wp = W[r][p2], wq = W[r][q2];
+          W[r][p2] = c2 * wp - s2 * wq;
+          W[r][q2] = s2 * wp + c2 * wq;
+        }
+      }
+      cur ^= 1;
+      __syncthreads();
+    }
+    total_rot += sweep_rot;
+    if (sweep_rot == 0) break;
+  }
+
+  if (total_rot > 0) {
+    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  thread (r = tid>>3, c4 = (tid&7)*4) computes 4 entries
+    const int r = tid >> 3, c0 = (tid & 7) * 4;
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+#pragma unroll 8
+    for (int k2 = 0; k2 < kD; ++k2) {
+      const double wr = W[k2][r];
+      t0 = fma(wr, W[k2][c0 + 0], t0);
+      t1 = fma(wr, W[k2][c0 + 1], t1);
+      t2 = fma(wr, W[k2][c0 + 2], t2);
+      t3 = fma(wr, W[k2][c0 + 3], t3);
+    }
+    T[r][c0 + 0] = (r == c0 + 0 ? 1.5 : 0.0) - 0.5 * t0;
+    T[r][c0 + 1] = (r == c0 + 1 ? 1.5 : 0.0) - 0.5 * t1;
+    T[r][c0 + 2] = (r == c0 + 2 ? 1.5 : 0.0) - 0.5 * t2;
+    T[r][c0 + 3] = (r == c0 + 3 ? 1.5 : 0.0) - 0.5 * t3;
+    // Output slot of W's column i: the slots that hold real columns, in order, receive the eigenvalues in
+    // descending order (stable).  Slots past the last column of a ragged block keep their (zero) column.
+    if (tid < kD) {
+      const Pair bp = sameh_pair(a.nb, k, pair);
+      const unsigned vmask = __ballot_sync(0xffffffffu, slot_col(bp.p, bp.q, tid, a.n) != kNoCol);
+      int out = tid;
+      if ((vmask >> tid) & 1u) {
+        const double di = Gb[cur][tid][tid];
+        int rk = 0;
+        for (int j = 0; j < kD; ++j) {
+          const double dj = Gb[cur][j][j];
+          rk += (((vmask >> j) & 1u) && (dj > di || (dj == di && j < (int)tid))) ? 1 : 0;
+        }
+        out = __fns(vmask, 0, rk + 1);  // position of the (rk+1)-th valid slot
+      }
+      rank_of[tid] = out;
+    }
+    __syncthreads();
+    double u0 = 0, u1 = 0, u2 = 0, u3 = 0;
+#pragma unroll 8
+    for (int k2 = 0; k2 < kD; ++k2) {
+      const double wr = W[r][k2];
+      u0 = fma(wr, T[k2][c0 + 0], u0);
+      u1 = fma(wr, T[k2][c0 + 1], u1);
+      u2 = fma(wr, T[k2][c0 + 2], u2);
+      u3 = fma(wr, T[k2][c0 + 3], u3);
+    }
+    double *wdst = wbuf + (size_t)pair * kD * kD;  // column-major: wdst[c*32 + r]
+    wdst[rank_of[c0 + 0] * kD + r] = u0;
+    wdst[rank_of[c0 + 1] * kD + r] = u1;
+    wdst[rank_of[c0 + 2] * kD + r] = u2;
+    wdst[rank_of[c0 + 3] * kD + r] = u3;
+  }
+  if (tid == 0) {
+    wflag[pair] = total_rot > 0 ? 1 : 0;
+    if (a.counters) {
+      if (total_rot > 0) atomicAdd(&a.counters->applied, (unsigned long long)total_rot);
+      atomicMax(&a.counters->offdiag_bits, fresh_max);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: X <- X W and Y <- Y W.  Each warp owns 8-row strips of the block pair's 32 columns (rows of A first,
+// then rows of V), reads a strip as 8 DMMA A-fragments, multiplies by W held in registers as 32
+// B-fragments, and writes the strip back in place (a strip depends only on itself).
+// ------------------------------------------------------------------------------------------------
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs a, const unsigned k,
+                                                                const double *__restrict__ wbuf,
+                                                                const int *__restrict__ wflag) {
+  if (!wflag[blockIdx.x]) return;  // nothing was rotated in this block pair: W = I
+  const Pair bp = sameh_pair(a.nb, k, blockIdx.x);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+
+  double wf[8][4];  // wf[ks][nt] = W[4 ks + tg][8 nt + g]
+  {
+    const double *w = wbuf + (size_t)blockIdx.x * kD * kD;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) wf[ks][nt] = w[(8 * nt + g) * kD + 4 * ks + tg];
+  }
+  unsigned lc[8];     // load columns: slot 4 ks + tg
+  unsigned sc[4][2];  // store columns: slot 8 nt + 2 tg + e
+#pragma unroll
+  for (int ks = 0; ks < 8; ++ks) lc[ks] = slot_col(bp.p, bp.q, 4 * ks + tg, a.n);
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    sc[nt][0] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg, a.n);
+    sc[nt][1] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg + 1, a.n);
+  }
+
+  const unsigned strips_a = (a.m + 7) >> 3;
+  const unsigned strips_v = a.rotate_v ? (a.vrows + 7) >> 3 : 0;
+  const unsigned total = strips_a + strips_v;
+  const unsigned stride = gridDim.y * WARPS;
+
+  auto load_strip = [&](unsigned s, double (&af)[8]) {
+    const bool isa = s < strips_a;
+    const double *base = isa ? a.A : a.V;
+    const size_t ld = isa ? a.lda : a.ldv;
+    const unsigned limit = isa ? a.m : a.vrows;
+    const unsigned row = (isa ? s : s - strips_a) * 8 + g;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks)
+      af[ks] = (row < limit && lc[ks] != kNoCol) ? base[(size_t)lc[ks] * ld + row] : 0.0;
+  };
+
+  unsigned s = blockIdx.y * WARPS + warp;
+  double cur[8], nxt[8];
+  if (s < total) load_strip(s, cur);
+  for (; s < total; s += stride) {
+    const unsigned sn = s + stride;
+    if (sn < total) load_strip(sn, nxt);
+    double d[4][2];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) d[nt][0] = d[nt][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) dmma884(d[nt][0], d[nt][1], cur[ks], wf[ks][nt]);
+    {
+      const bool isa = s < strips_a;
+      double *base = isa ? a.A : a.V;
+      const size_t ld = isa ? a.lda : a.ldv;
+      const unsigned limit = isa ? a.m : a.vrows;
+      const unsigned row = (isa ? s : s - strips_a) * 8 + g;
+      if (row < limit) {
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          if (sc[nt][0] != kNoCol) base[(size_t)sc[nt][0] * ld + row] = d[nt][0];
+          if (sc[nt][1] != kNoCol) base[(size_t)sc[nt][1] * ld + row] = d[nt][1];
+        }
+      }
+    }
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) cur[ks] = nxt[ks];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static constexpr int kGramWarps = 4, kGramUnroll = 4, kUpdWarps = 4;
+
+unsigned blk_num_blocks(size_t n) { return (unsigned)((n + kBW - 1) / kBW); }
+
+static unsigned gram_splits(size_t m, unsigned pairs) {
+  // about 8 CTAs per SM, at least 64 rows (one unrolled iteration) per CTA
+  size_t want = (8 * 148 + pairs - 1) / (pairs ? pairs : 1);
+  size_t cap = (m + 63) / 64;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  if (want > 1024) want = 1024;
+  return (unsigned)want;
+}
+
+void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
+  const unsigned nb = blk_num_blocks(n);
+  const unsigned pairs = nb / 2;
+  *gpart_doubles = (size_t)pairs * gram_splits(m, pairs) * kGramPart;
+  *w_doubles = (size_t)pairs * kD * kD;
+  *flag_ints = pairs;
+}
+
+int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
+                    unsigned long long *launches) {
+  const unsigned pairs = a.nb / 2;
+  if (pairs == 0) return SVDJ_OK;
+  const unsigned splits = gram_splits(a.m, pairs);
+  unsigned rps = (a.m + splits - 1) / splits;
+  rps = (rps + 3u) & ~3u;  // k-steps are 4 rows
+  blk_gram_kernel<kGramWarps, kGramUnroll><<<dim3(pairs, splits), kGramWarps * 32, 0, st>>>(a, k, rps, gpart);
+  blk_eig_kernel<<<pairs, 256, 0, st>>>(a, k, splits, gpart, wbuf, wflag);
+  const unsigned strips = ((a.m + 7) >> 3) + (a.rotate_v ? ((a.vrows + 7) >> 3) : 0);
+  unsigned usplits = (8 * 148 + pairs - 1) / pairs;
+  const unsigned ucap = (strips + kUpdWarps * 4 - 1) / (kUpdWarps * 4);  // >= 4 strips per warp
+  if (usplits > ucap) usplits = ucap;
+  if (usplits < 1) usplits = 1;
+  blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag);
+  if (launches) *launches += 3;
+  SVDJ_CUDA_TRY(cudaGetLastError());
+  return SVDJ_OK;
+}
+
+}  // namespace svdj

@@ -161,6 +161,27 @@ int l1_launch_split(const StepArgs &a, unsigned k, double *scratch, cudaStream_t
 bool l1_uses_split(size_t m, size_t n);
 size_t l1_scratch_doubles(size_t m, size_t n);
 
+// Block-Jacobi step (svdj_block.cu): column blocks of 16, block pairs in the same round-robin ordering.
+struct BlockArgs {
+  double *A;
+  size_t lda;
+  double *V;
+  size_t ldv;
+  unsigned m, n;
+  unsigned vrows;
+  int rotate_v;
+  unsigned nb;  // number of column blocks, ceil(n / 16)
+  double tol;
+  int threshold_mode;
+  int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
+  SweepCounters *counters;  // may be null
+};
+unsigned blk_num_blocks(size_t n);
+void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
+// k = 1-based step of the round-robin ordering over the nb blocks
+int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
+                    unsigned long long *launches);
+
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st);
 int launch_column_norms(const double *A, size_t lda, size_t m, size_t n, double *norms, cudaStream_t st);

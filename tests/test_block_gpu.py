@@ -1,0 +1,133 @@
+"""GPU parity tests of the block-Jacobi variant (FP64 DMMA tiles), through the C ABI.
+
+The block path rotates the same column pairs as the level-1 path but 32 columns at a time, from Gram
+entries, so its rotation sequence differs from the reference's: parity is on the converged result, with the
+tolerances of BASELINE.json (stated in tests/test_l1_gpu.py): sigma <= 1e-12 normwise against the oracle and
+LAPACK, U and V up to sign where sigma is separated, orthogonality and residual <= 10*max(m,n)*eps.
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _solve(svdj, A0, variant, **kw):
+    m, n = A0.shape
+    A = A0.copy(order="F")
+    s = np.zeros(min(m, n))
+    V = np.zeros((n, n), order="F")
+    st = svdj.dgesvd(svdj.AllVec, svdj.AllVec, m, n, A, m, s, V, n, svdj.default_opts(variant=variant, **kw))
+    return A, s, V, st
+
+
+# 120 and 100 columns: ragged last block; 37 columns: odd number of blocks (one idles per step)
+@pytest.mark.parametrize("m,n", [(64, 64), (200, 120), (130, 37), (257, 64), (512, 512), (1000, 100), (96, 33)])
+def test_block_solve_matches_oracle_and_lapack(svdj, m, n):
+    A0 = H.uniform_matrix(m, n, seed=m * 7 + n)
+    Uo, so, Vo, ost, orc = H.oracle_svd(A0)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st.variant == svdj.VARIANT_BLOCK and st.converged == 1
+    assert st.sweeps <= ost.sweeps + 1, (st.sweeps, ost.sweeps)
+    assert H.sigma_error_normwise(s, so) <= 1e-12
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    assert np.all(np.diff(s) <= 0)
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * max(m, n) * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+    Ug, Vg = H.fix_signs(A, V)
+    Uo2, Vo2 = H.fix_signs(Uo, Vo)
+    gap = np.minimum(np.abs(np.diff(so, prepend=np.inf)), np.abs(np.diff(so, append=0.0))) / so[0]
+    well = gap > 1e-3
+    assert np.abs(Vg[:, well] - Vo2[:, well]).max() <= 1e-8
+    assert np.abs(Ug[:, : len(so)][:, well] - Uo2[:, : len(so)][:, well]).max() <= 1e-8
+
+
+def test_block_and_level1_agree(svdj):
+    A0 = H.normal_matrix(300, 160, seed=8)
+    A1, s1, V1, st1 = _solve(svdj, A0, svdj.VARIANT_LEVEL1)
+    A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st1.variant == svdj.VARIANT_LEVEL1 and st2.variant == svdj.VARIANT_BLOCK
+    assert H.sigma_error_normwise(s2, s1) <= 1e-12
+    U1, W1 = H.fix_signs(A1, V1)
+    U2, W2 = H.fix_signs(A2, V2)
+    assert np.abs(W1 - W2).max() <= 1e-9 and np.abs(U1 - U2).max() <= 1e-9
+
+
+def test_block_ill_conditioned(svdj):
+    n = 256
+    A0, sigma = H.prescribed_spectrum(n, 1e12, seed=5, cluster=True)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st.converged == 1
+    assert H.sigma_error_normwise(s, np.sort(sigma)[::-1]) <= 1e-12
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * n * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+
+
+def test_block_edge_cases(svdj):
+    # zero matrix: nothing rotates, V = I
+    A, s, V, st = _solve(svdj, np.zeros((80, 64), order="F"), svdj.VARIANT_BLOCK)
+    assert st.converged == 1 and np.all(s == 0) and np.array_equal(V, np.eye(64))
+    # rank deficient: duplicate columns spread over different blocks
+    B = H.uniform_matrix(90, 40, seed=1)
+    A0 = np.asfortranarray(np.hstack([B, B[:, :30]]))
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    assert np.linalg.norm(A0 - (A * s) @ V.T) <= 10 * 90 * H.EPS * np.linalg.norm(A0)
+    assert np.all(s[40:] <= 1e-12 * s[0])
+    # fewer than two blocks: the block variant hands over to the level-1 path
+    A0 = H.uniform_matrix(40, 12, seed=2)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st.variant == svdj.VARIANT_LEVEL1
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    # NoVec / NoVec
+    A0 = H.uniform_matrix(128, 96, seed=3)
+    A = A0.copy(order="F")
+    s = np.zeros(96)
+    V = np.full((96, 96), 5.0, order="F")
+    svdj.dgesvd(svdj.NoVec, svdj.NoVec, 128, 96, A, 128, s, V, 96, svdj.default_opts(variant=svdj.VARIANT_BLOCK))
+    assert np.all(V == 5.0) and H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    assert np.allclose(np.linalg.norm(A, axis=0), s, rtol=1e-13)
+
+
+def test_auto_picks_block_for_wide_problems_and_level1_for_reference_mode(svdj):
+    A0 = H.uniform_matrix(128, 128, seed=5)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_AUTO)
+    assert st.variant == svdj.VARIANT_BLOCK
+    A = A0.copy(order="F")
+    st = svdj.cuda_dgesvd_kernel(0, 0, 128, 128, A, 128, np.zeros(128), np.zeros((128, 128), order="F"), 128,
+                                 reference_mode=True)
+    assert st.variant == svdj.VARIANT_LEVEL1 and st.sweeps == 1
+
+
+def test_block_tall_skinny(svdj):
+    m, n = 50000, 64
+    A0 = H.normal_matrix(m, n, seed=2)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st.converged == 1
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(A0, A, s, V)
+    assert q["orth_u"] <= 10 * m * H.EPS and q["orth_v"] <= 10 * n * H.EPS and q["resid"] <= 10 * n * H.EPS
+
+
+def test_block_full_size_4096_properties(svdj):
+    n = 4096
+    A0 = H.uniform_matrix(n, n, seed=4096)
+    dA = torch.from_numpy(np.ascontiguousarray(A0.T)).cuda()
+    dA0 = dA.clone()
+    ds = torch.zeros(n, dtype=torch.float64, device="cuda")
+    dV = torch.empty(n, n, dtype=torch.float64, device="cuda")
+    st = svdj.dgesvd_device(0, 0, n, n, dA.data_ptr(), n, ds.data_ptr(), dV.data_ptr(), n,
+                            svdj.default_opts(variant=svdj.VARIANT_BLOCK))
+    assert st.converged == 1 and st.sweeps <= 25
+    ref = torch.linalg.svdvals(dA0.T)
+    assert float((ds - ref).abs().max() / ref[0]) <= 1e-12
+    U, V = dA.T, dV.T
+    eye = torch.eye(n, dtype=torch.float64, device="cuda")
+    bound = 10 * n * H.EPS
+    assert float((U.T @ U - eye).abs().max()) <= bound
+    assert float((V.T @ V - eye).abs().max()) <= bound
+    assert float(torch.linalg.norm(dA0.T - (U * ds) @ V.T) / torch.linalg.norm(dA0)) <= bound

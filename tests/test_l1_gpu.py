@@ -91,7 +91,7 @@ def test_solve_matches_oracle_and_lapack(svdj, m, n):
     A = A0.copy(order="F")
     s = np.zeros(min(m, n))
     V = np.zeros((n, n), order="F")
-    st = svdj.cuda_dgesvd_kernel(svdj.AllVec, svdj.AllVec, m, n, A, m, s, V, n)
+    st = svdj.cuda_dgesvd_kernel(svdj.AllVec, svdj.AllVec, m, n, A, m, s, V, n, variant=svdj.VARIANT_LEVEL1)
     assert st.converged == 1
     assert abs(st.sweeps - ost.sweeps) <= 1, (st.sweeps, ost.sweeps)
     assert H.sigma_error_normwise(s, so) <= 1e-12
@@ -115,7 +115,7 @@ def test_ill_conditioned_prescribed_spectrum(svdj):
     A = A0.copy(order="F")
     s = np.zeros(n)
     V = np.zeros((n, n), order="F")
-    st = svdj.cuda_dgesvd_kernel(0, 0, n, n, A, n, s, V, n)
+    st = svdj.cuda_dgesvd_kernel(0, 0, n, n, A, n, s, V, n, variant=svdj.VARIANT_LEVEL1)
     assert st.converged == 1
     assert H.sigma_error_normwise(s, np.sort(sigma)[::-1]) <= 1e-12
     q = H.svd_quality(A0, A, s, V)
@@ -208,7 +208,7 @@ def test_tall_skinny_uses_split_path(svdj):
     A = A0.copy(order="F")
     s = np.zeros(n)
     V = np.zeros((n, n), order="F")
-    st = svdj.cuda_dgesvd_kernel(0, 0, m, n, A, m, s, V, n)
+    st = svdj.cuda_dgesvd_kernel(0, 0, m, n, A, m, s, V, n, variant=svdj.VARIANT_LEVEL1)
     assert st.converged == 1
     assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
     q = H.svd_quality(A0, A, s, V)
@@ -223,7 +223,7 @@ def test_full_size_4096_properties(svdj):
     A = A0.copy(order="F")
     s = np.zeros(n)
     V = np.zeros((n, n), order="F")
-    st = svdj.cuda_dgesvd_kernel(0, 0, n, n, A, n, s, V, n)
+    st = svdj.cuda_dgesvd_kernel(0, 0, n, n, A, n, s, V, n, variant=svdj.VARIANT_LEVEL1)
     assert st.converged == 1 and st.sweeps <= 25
     ref = torch.linalg.svdvals(torch.from_numpy(A0).cuda()).cpu().numpy()
     assert H.sigma_error_normwise(s, ref) <= 1e-12
