@@ -83,8 +83,10 @@ typedef struct svdj_stats {
   double seconds_h2d;            /* host->device copies (svdj_dgesvd only) */
   double seconds_d2h;            /* device->host copies (svdj_dgesvd only) */
   double seconds_total;          /* wall time of the call */
-  double step_kernel_ms;         /* mean device time of the dominant sweep kernel (per launch) */
-  unsigned long long step_kernel_launches; /* launches of that kernel */
+  double step_kernel_ms;         /* mean device time per launch of the dominant sweep kernel: the fused level-1
+                                    step, or the block path's update kernel (probed with events every 8th step) */
+  unsigned long long step_kernel_launches; /* launches of that kernel (block path: the probed ones) */
+  unsigned long long probe_block_pairs;    /* block path: block pairs updated by the probed launches */
 } svdj_stats;
 
 /* Fills *opts with the defaults described above. */

@@ -64,6 +64,7 @@ class Stats(C.Structure):
         ("seconds_total", C.c_double),
         ("step_kernel_ms", C.c_double),
         ("step_kernel_launches", C.c_ulonglong),
+        ("probe_block_pairs", C.c_ulonglong),
     ]
 
     def as_dict(self) -> dict:

@@ -220,16 +220,42 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   a.tol = o.tol;
   a.threshold_mode = o.threshold_mode;
 
+  // probes of the block path's update kernel
+  constexpr int kProbes = 256;
+  std::vector<Event> probe_events(block ? 2 * kProbes : 0);
+  std::vector<BlockProbe> probes(block ? kProbes : 0);
+  DevBuf d_probe;
+  int probes_used = 0;
+  double probe_ms = 0.0;
+  unsigned long long probe_launches = 0;
+  if (block) {
+    if (int rc = d_probe.alloc(sizeof(unsigned long long))) return rc;
+    SVDJ_CUDA_TRY(cudaMemsetAsync(d_probe.p, 0, sizeof(unsigned long long), stream));
+    for (int i = 0; i < kProbes; ++i) {
+      if (int rc = probe_events[2 * i].create()) return rc;
+      if (int rc = probe_events[2 * i + 1].create()) return rc;
+      probes[i].before = probe_events[2 * i].e;
+      probes[i].after = probe_events[2 * i + 1].e;
+    }
+  }
+
   SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, stream));
   unsigned long long step_launches = 0;
   bool converged = false;
+  const bool trace = std::getenv("SVDJ_TRACE") != nullptr;  // per-sweep progress on stderr
   for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
     a.counters = d_counters.as<SweepCounters>() + sweep;
     b.counters = a.counters;
     for (unsigned k = 1; k <= steps; ++k) {
       if (block) {
+        // every 8th step carries a probe around its update kernel (events + pairs really updated)
+        const BlockProbe *probe = nullptr;
+        if (k % 8 == 1 && probes_used < kProbes) {
+          probes[probes_used].active_pairs = d_probe.as<unsigned long long>();
+          probe = &probes[probes_used++];
+        }
         if (int rc = blk_launch_step(b, k, d_gpart.as<double>(), d_w.as<double>(), d_wflag.as<int>(), stream,
-                                     &step_launches))
+                                     &step_launches, probe))
           return rc;
       } else {
         if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
@@ -237,6 +263,13 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     }
     SVDJ_CUDA_TRY(cudaMemcpyAsync(h_counters.p, a.counters, sizeof(SweepCounters), cudaMemcpyDeviceToHost, stream));
     SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+    for (int i = 0; i < probes_used; ++i) {
+      float ms = 0.f;
+      SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms, probes[i].before, probes[i].after));
+      probe_ms += ms;
+    }
+    probe_launches += (unsigned long long)probes_used;
+    probes_used = 0;
     const SweepCounters *hc = h_counters.as<SweepCounters>();
     st.sweeps = sweep + 1;
     st.tested += pairs_per_step * steps;
@@ -244,6 +277,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     double off;
     std::memcpy(&off, &hc->offdiag_bits, sizeof(double));
     st.last_offdiag = off;
+    if (trace) {
+      std::fprintf(stderr, "[svdj] sweep %2d: rotations %llu, max off-diagonal cosine %.3e (tol %.3e)\n", sweep + 1,
+                   (unsigned long long)hc->applied, off, o.tol);
+    }
     if (hc->applied == 0) {
       converged = true;
       break;
@@ -307,6 +344,15 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   st.seconds_sweeps = ms01 * 1e-3;
   st.seconds_finalize = ms12 * 1e-3;
   st.step_kernel_ms = step_launches ? (double)ms01 / (double)step_launches : 0.0;
+  if (block) {
+    // dominant kernel of the block path = the update kernel: mean of the probed launches, and the block
+    // pairs those launches updated (each moves 512 (m + n) bytes: 32 columns of A and V read and written)
+    unsigned long long active = 0;
+    SVDJ_CUDA_TRY(cudaMemcpy(&active, d_probe.p, sizeof(active), cudaMemcpyDeviceToHost));
+    st.step_kernel_ms = probe_launches ? probe_ms / (double)probe_launches : 0.0;
+    st.step_kernel_launches = probe_launches;
+    st.probe_block_pairs = active;
+  }
   if (o.threshold_mode == SVDJ_THRESH_REL && !converged) return SVDJ_NOT_CONVERGED;
   return SVDJ_OK;
 }

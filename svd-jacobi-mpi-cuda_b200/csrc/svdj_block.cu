@@ -13,6 +13,8 @@
 // One block pair covers b(2b-1) = 496 column pairs for 16b(3m+2n) bytes of traffic, against 32(m+n) per
 // pair on the level-1 path: ~0.8 b = 13x fewer bytes per sweep; flops rise to 10 n^3 per sweep (m = n).
 // tcgen05 has no FP64 kind, so mma.sync DMMA is the sm_100a FP64 tensor path (profiles/r1_fp64_peaks.md).
+#include <cstdlib>
+
 #include "svdj_common.cuh"
 
 namespace svdj {
@@ -380,9 +382,169 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
 }
 
 // ------------------------------------------------------------------------------------------------
+// K3, staged: the same update for aligned layouts (even leading dimensions, 16-byte aligned bases).
+// Persistent CTAs (4 per SM) walk a flat list of 64-row x 32-column tiles of the block pairs that
+// rotated (compacted from wflag), so the grid is a multiple of the SM count and nothing is spent on
+// pairs whose W is the identity.  Tiles are brought into shared memory by a 3-stage cp.async
+// pipeline: every warp-level copy is one column's 512 contiguous bytes, no registers are tied up by
+// loads in flight, and ~100 KB per SM are outstanding -- the plain kernel above is latency-bound
+// at 17 % occupancy (profiles/r1_block_4096.md).  Column stride 68 doubles makes the DMMA
+// A-fragment reads (4 columns x 8 rows per warp) bank-conflict free.
+// ------------------------------------------------------------------------------------------------
+static constexpr int kTileRows = 64;
+static constexpr int kTileStride = kTileRows + 4;
+static constexpr int kTileDoubles = kD * kTileStride;
+static constexpr int kUpdStages = 3;
+static constexpr int kMaxCompactPairs = 2048;
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, int src_bytes) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockArgs a, const unsigned k,
+                                                                  const double *__restrict__ wbuf,
+                                                                  const int *__restrict__ wflag,
+                                                                  const unsigned pairs,
+                                                                  unsigned long long *__restrict__ active_out) {
+  extern __shared__ __align__(16) double tiles[];  // STAGES x 32 columns x kTileStride
+  __shared__ unsigned short active[kMaxCompactPairs];
+  __shared__ unsigned n_active_s;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+
+  if (warp == 0) {  // compact the block pairs that rotated
+    unsigned cnt = 0;
+    for (unsigned base = 0; base < pairs; base += 32) {
+      const unsigned p = base + lane;
+      const bool f = p < pairs && wflag[p] != 0;
+      const unsigned mask = __ballot_sync(0xffffffffu, f);
+      if (f) active[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)p;
+      cnt += __popc(mask);
+    }
+    if (lane == 0) {
+      n_active_s = cnt;
+      if (active_out != nullptr && blockIdx.x == 0) *active_out += cnt;
+    }
+  }
+  __syncthreads();
+  const unsigned n_active = n_active_s;
+  const unsigned tpa = (a.m + kTileRows - 1) / kTileRows;
+  const unsigned tpv = a.rotate_v ? (a.vrows + kTileRows - 1) / kTileRows : 0;
+  const unsigned tpp = tpa + tpv;
+  const unsigned long long total = (unsigned long long)n_active * tpp;
+  const unsigned t0 = (unsigned)(total * blockIdx.x / gridDim.x);
+  const unsigned t1 = (unsigned)(total * (blockIdx.x + 1) / gridDim.x);
+  if (t0 >= t1) return;
+
+  auto issue_tile = [&](unsigned tau, int stage) {
+    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+    const Pair bp = sameh_pair(a.nb, k, active[ap]);
+    const bool isa = t < tpa;
+    const double *base = isa ? a.A : a.V;
+    const size_t ld = isa ? a.lda : a.ldv;
+    const unsigned limit = isa ? a.m : a.vrows;
+    const unsigned row = (isa ? t : t - tpa) * kTileRows + 2 * lane;
+    double *dst = tiles + stage * kTileDoubles + 2 * lane;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const unsigned slot = warp + 4 * i;
+      const unsigned col = slot_col(bp.p, bp.q, slot, a.n);
+      int bytes = 0;
+      const double *src = base;
+      if (col != kNoCol && row < limit) {
+        bytes = (row + 1 < limit) ? 16 : 8;
+        src = base + (size_t)col * ld + row;
+      }
+      cp_async16(dst + slot * kTileStride, src, bytes);
+    }
+  };
+
+  unsigned issued = t0;
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (issued < t1) {
+      issue_tile(issued, s);
+      ++issued;
+    }
+    cp_async_commit();
+  }
+
+  double wf[8][4];
+  unsigned sc[4][2];
+  unsigned cur_pair = 0xffffffffu;
+  for (unsigned tau = t0; tau < t1; ++tau) {
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();  // tile tau has landed for everyone; everyone is done with the stage refilled next
+    if (issued < t1) {
+      issue_tile(issued, (int)((issued - t0) % STAGES));
+      ++issued;
+    }
+    cp_async_commit();
+
+    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+    const unsigned pr = active[ap];
+    if (pr != cur_pair) {  // new block pair: its W (B fragments) and the columns this lane stores to
+      cur_pair = pr;
+      const Pair bp = sameh_pair(a.nb, k, pr);
+      const double *w = wbuf + (size_t)pr * kD * kD;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) wf[ks][nt] = w[(8 * nt + g) * kD + 4 * ks + tg];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        sc[nt][0] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg, a.n);
+        sc[nt][1] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg + 1, a.n);
+      }
+    }
+    const bool isa = t < tpa;
+    double *base = isa ? a.A : a.V;
+    const size_t ld = isa ? a.lda : a.ldv;
+    const unsigned limit = isa ? a.m : a.vrows;
+    const unsigned row0 = (isa ? t : t - tpa) * kTileRows + 16 * warp;
+    const double *tile = tiles + ((tau - t0) % STAGES) * kTileDoubles + 16 * warp + g;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      double af[8];
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) af[ks] = tile[(4 * ks + tg) * kTileStride + 8 * h];
+      double d[4][2];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) d[nt][0] = d[nt][1] = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) dmma884(d[nt][0], d[nt][1], af[ks], wf[ks][nt]);
+      const unsigned row = row0 + 8 * h + g;
+      if (row < limit) {
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          if (sc[nt][0] != kNoCol) base[(size_t)sc[nt][0] * ld + row] = d[nt][0];
+          if (sc[nt][1] != kNoCol) base[(size_t)sc[nt][1] * ld + row] = d[nt][1];
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 static constexpr int kGramWarps = 4, kGramUnroll = 4, kUpdWarps = 4;
+
+// SVDJ_BLOCK_PLAIN=1 forces the unstaged kernels (used by the tests to cover both code paths)
+static bool blk_force_plain_update() {
+  const char *e = std::getenv("SVDJ_BLOCK_PLAIN");
+  return e != nullptr && e[0] == '1';
+}
 
 unsigned blk_num_blocks(size_t n) { return (unsigned)((n + kBW - 1) / kBW); }
 
@@ -405,7 +567,7 @@ void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doub
 }
 
 int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                    unsigned long long *launches) {
+                    unsigned long long *launches, const BlockProbe *probe) {
   const unsigned pairs = a.nb / 2;
   if (pairs == 0) return SVDJ_OK;
   const unsigned splits = gram_splits(a.m, pairs);
@@ -418,7 +580,25 @@ int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf,
   const unsigned ucap = (strips + kUpdWarps * 4 - 1) / (kUpdWarps * 4);  // >= 4 strips per warp
   if (usplits > ucap) usplits = ucap;
   if (usplits < 1) usplits = 1;
-  blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag);
+  const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
+                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0)));
+  if (aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update()) {
+    static const int sm_count = [] {
+      int dev = 0, n = 148;
+      if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+      return n;
+    }();
+    constexpr size_t smem = sizeof(double) * kUpdStages * kTileDoubles;
+    static const cudaError_t attr = cudaFuncSetAttribute(blk_update_staged_kernel<kUpdStages>,
+                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    SVDJ_CUDA_TRY(attr);
+    if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
+    blk_update_staged_kernel<kUpdStages><<<sm_count * 4, 128, smem, st>>>(a, k, wbuf, wflag, pairs,
+                                                                          probe ? probe->active_pairs : nullptr);
+    if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  } else {
+    blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag);
+  }
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());
   return SVDJ_OK;

@@ -176,11 +176,17 @@ struct BlockArgs {
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
   SweepCounters *counters;  // may be null
 };
+// Optional timing of the update kernel (the dominant, HBM-bound one) of a step: events recorded around it
+// and a device counter that receives the number of block pairs it really updated.
+struct BlockProbe {
+  cudaEvent_t before = nullptr, after = nullptr;
+  unsigned long long *active_pairs = nullptr;
+};
 unsigned blk_num_blocks(size_t n);
 void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
 // k = 1-based step of the round-robin ordering over the nb blocks
 int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                    unsigned long long *launches);
+                    unsigned long long *launches, const BlockProbe *probe = nullptr);
 
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st);
