@@ -156,6 +156,31 @@ int svdj_step_device_noalloc(size_t m, size_t n, double *dA, size_t lda, double 
                              int rotate_v, size_t step, double tol, int threshold_mode,
                              unsigned long long *d_counters, void *stream);
 
+/*
+ * Per-rank compute of the multi-GPU solver.  These replace what a non-root rank does between the
+ * reference's MPI_Recv and MPI_Send (main.cu:769-850: Gram triples, rotation parameters and rotations
+ * of the pairs whose columns it was sent) -- except that the rank keeps its columns: two column blocks of
+ * w columns each ("left" and "right": A-blocks m x w, V-blocks vrows x w, column-major, in separate
+ * allocations so that one can travel to a ring neighbour while the other stays).
+ *
+ * svdj_ring_ws_create / _destroy: scratch for 2w local columns (w a multiple of 16).
+ * svdj_ring_phase_device: SVDJ_PHASE_ALL orthogonalises every pair of the 2w local columns (one local
+ *   block-Jacobi sweep); SVDJ_PHASE_CROSS only the pairs with one column in each buffer (what is left to do
+ *   when both blocks have already been swept internally in this sweep).  d_counters (2 x unsigned long
+ *   long on the device, may be NULL) accumulates [0] += rotations, [1] = max(bits of off-diagonal cosine).
+ *   inner_sweeps <= 0 selects the default (2).
+ * svdj_ring_finalize_device: sigma = column norms of the local columns and, if scale_u, U = A / sigma in
+ *   place (main.cu:1395-1411, on the device and per rank).
+ */
+enum { SVDJ_PHASE_ALL = 0, SVDJ_PHASE_CROSS = 1 };
+int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out);
+int svdj_ring_ws_destroy(void *ws);
+int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right,
+                           size_t lda, double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase,
+                           double tol, int inner_sweeps, unsigned long long *d_counters, void *stream);
+int svdj_ring_finalize_device(void *ws, size_t m, size_t ncols, double *dA, size_t lda, double *d_sigma,
+                              int scale_u, void *stream);
+
 /* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
 size_t svdj_num_steps(size_t n);
 

@@ -25,6 +25,7 @@ AllVec, SomeVec, NoVec = 0, 1, 2
 VARIANT_AUTO, VARIANT_LEVEL1, VARIANT_BLOCK = 0, 1, 2
 THRESH_REL, THRESH_ABS = 0, 1
 PATH_AUTO, PATH_REG, PATH_SPLIT = 0, 1, 2
+PHASE_ALL, PHASE_CROSS = 0, 1
 OK, NOT_CONVERGED, ERR_CUDA, ERR_ALLOC, ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 
 
@@ -79,6 +80,10 @@ EXPORTS = (
     "svdj_step_device",
     "svdj_step_scratch_doubles",
     "svdj_step_device_noalloc",
+    "svdj_ring_ws_create",
+    "svdj_ring_ws_destroy",
+    "svdj_ring_phase_device",
+    "svdj_ring_finalize_device",
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_last_error",
@@ -104,6 +109,14 @@ def _load() -> C.CDLL:
     lib.svdj_step_device.restype = i
     lib.svdj_step_device_noalloc.argtypes = [sz, sz, vp, sz, vp, sz, i, sz, dbl, i, vp, vp]
     lib.svdj_step_device_noalloc.restype = i
+    lib.svdj_ring_ws_create.argtypes = [sz, sz, C.POINTER(C.c_void_p)]
+    lib.svdj_ring_ws_create.restype = i
+    lib.svdj_ring_ws_destroy.argtypes = [vp]
+    lib.svdj_ring_ws_destroy.restype = i
+    lib.svdj_ring_phase_device.argtypes = [vp, sz, sz, sz, vp, vp, sz, vp, vp, sz, i, i, dbl, i, vp, vp]
+    lib.svdj_ring_phase_device.restype = i
+    lib.svdj_ring_finalize_device.argtypes = [vp, sz, sz, vp, sz, vp, i, vp]
+    lib.svdj_ring_finalize_device.restype = i
     lib.svdj_step_scratch_doubles.argtypes = [sz, sz]
     lib.svdj_step_scratch_doubles.restype = sz
     lib.svdj_num_steps.argtypes = [sz]

@@ -38,6 +38,26 @@ __device__ __forceinline__ unsigned slot_col(unsigned I, unsigned J, unsigned s,
   return c < n ? c : kNoCol;
 }
 
+// Columns live in up to two buffers (multi-GPU drivers keep the two column blocks that a rank holds in
+// separate allocations so that one can travel while the other stays): column c < split is in the first.
+__device__ __forceinline__ double *col_ptr(const BlockArgs &a, bool is_a, unsigned c) {
+  // A2 / V2 arrive pre-biased by -split * ld (blk_launch_step), so both halves index with c itself
+  double *base = is_a ? (c < a.split ? a.A : a.A2) : (c < a.split ? a.V : a.V2);
+  return base + (size_t)c * (is_a ? a.lda : a.ldv);
+}
+
+// Block pair idx of step k (1-based).  sched 0: the reference's round-robin over all nb blocks
+// (every pair once per nb-1 steps); sched 1: bipartite, block i of the first half with block
+// (i + k - 1) mod (nb/2) of the second half (every cross pair once per nb/2 steps).
+__device__ __forceinline__ Pair block_pair(const BlockArgs &a, unsigned k, unsigned idx) {
+  if (a.sched == 0) return sameh_pair(a.nb, k, idx);
+  const unsigned half = a.nb >> 1;
+  Pair r;
+  r.p = idx;
+  r.q = half + (idx + k - 1u) % half;
+  return r;
+}
+
 // ------------------------------------------------------------------------------------------------
 // K1: partial Gram matrices.  grid (block pairs, row splits); each warp walks 4-row k-steps of its
 // rows.  For G = X^T X the A fragment of tile row ti and the B fragment of tile column tj are the same
@@ -49,7 +69,7 @@ __global__ void __launch_bounds__(WARPS * 32) blk_gram_kernel(const BlockArgs a,
                                                               const unsigned rows_per_split,
                                                               double *__restrict__ gpart) {
   __shared__ double red[WARPS][kGramPart];
-  const Pair bp = sameh_pair(a.nb, k, blockIdx.x);
+  const Pair bp = block_pair(a, k, blockIdx.x);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned g = lane >> 2, tg = lane & 3;
   const double *cp[4];
@@ -58,7 +78,7 @@ __global__ void __launch_bounds__(WARPS * 32) blk_gram_kernel(const BlockArgs a,
   for (int gi = 0; gi < 4; ++gi) {
     const unsigned c = slot_col(bp.p, bp.q, 8 * gi + g, a.n);
     cv[gi] = (c != kNoCol);
-    cp[gi] = a.A + (size_t)(cv[gi] ? c : 0) * a.lda;
+    cp[gi] = col_ptr(a, true, cv[gi] ? c : 0);
   }
   const unsigned r0 = blockIdx.y * rows_per_split;
   const unsigned r1 = min(a.m, r0 + rows_per_split);
@@ -262,7 +282,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     // Output slot of W's column i: the slots that hold real columns, in order, receive the eigenvalues in
     // descending order (stable).  Slots past the last column of a ragged block keep their (zero) column.
     if (tid < kD) {
-      const Pair bp = sameh_pair(a.nb, k, pair);
+      const Pair bp = block_pair(a, k, pair);
       const unsigned vmask = __ballot_sync(0xffffffffu, slot_col(bp.p, bp.q, tid, a.n) != kNoCol);
       int out = tid;
       if ((vmask >> tid) & 1u) {
@@ -311,7 +331,7 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
                                                                 const double *__restrict__ wbuf,
                                                                 const int *__restrict__ wflag) {
   if (!wflag[blockIdx.x]) return;  // nothing was rotated in this block pair: W = I
-  const Pair bp = sameh_pair(a.nb, k, blockIdx.x);
+  const Pair bp = block_pair(a, k, blockIdx.x);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned g = lane >> 2, tg = lane & 3;
 
@@ -340,13 +360,11 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
 
   auto load_strip = [&](unsigned s, double (&af)[8]) {
     const bool isa = s < strips_a;
-    const double *base = isa ? a.A : a.V;
-    const size_t ld = isa ? a.lda : a.ldv;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row = (isa ? s : s - strips_a) * 8 + g;
 #pragma unroll
     for (int ks = 0; ks < 8; ++ks)
-      af[ks] = (row < limit && lc[ks] != kNoCol) ? base[(size_t)lc[ks] * ld + row] : 0.0;
+      af[ks] = (row < limit && lc[ks] != kNoCol) ? col_ptr(a, isa, lc[ks])[row] : 0.0;
   };
 
   unsigned s = blockIdx.y * WARPS + warp;
@@ -364,15 +382,13 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
       for (int nt = 0; nt < 4; ++nt) dmma884(d[nt][0], d[nt][1], cur[ks], wf[ks][nt]);
     {
       const bool isa = s < strips_a;
-      double *base = isa ? a.A : a.V;
-      const size_t ld = isa ? a.lda : a.ldv;
       const unsigned limit = isa ? a.m : a.vrows;
       const unsigned row = (isa ? s : s - strips_a) * 8 + g;
       if (row < limit) {
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-          if (sc[nt][0] != kNoCol) base[(size_t)sc[nt][0] * ld + row] = d[nt][0];
-          if (sc[nt][1] != kNoCol) base[(size_t)sc[nt][1] * ld + row] = d[nt][1];
+          if (sc[nt][0] != kNoCol) col_ptr(a, isa, sc[nt][0])[row] = d[nt][0];
+          if (sc[nt][1] != kNoCol) col_ptr(a, isa, sc[nt][1])[row] = d[nt][1];
         }
       }
     }
@@ -395,6 +411,7 @@ static constexpr int kTileRows = 64;
 static constexpr int kTileStride = kTileRows + 4;
 static constexpr int kTileDoubles = kD * kTileStride;
 static constexpr int kUpdStages = 3;
+static constexpr int kUpdCtasPerSm = 4;
 static constexpr int kMaxCompactPairs = 2048;
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, int src_bytes) {
@@ -408,7 +425,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 template <int STAGES>
-__global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockArgs a, const unsigned k,
+__global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(const BlockArgs a, const unsigned k,
                                                                   const double *__restrict__ wbuf,
                                                                   const int *__restrict__ wflag,
                                                                   const unsigned pairs,
@@ -445,10 +462,8 @@ __global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockAr
 
   auto issue_tile = [&](unsigned tau, int stage) {
     const unsigned ap = tau / tpp, t = tau - ap * tpp;
-    const Pair bp = sameh_pair(a.nb, k, active[ap]);
+    const Pair bp = block_pair(a, k, active[ap]);
     const bool isa = t < tpa;
-    const double *base = isa ? a.A : a.V;
-    const size_t ld = isa ? a.lda : a.ldv;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row = (isa ? t : t - tpa) * kTileRows + 2 * lane;
     double *dst = tiles + stage * kTileDoubles + 2 * lane;
@@ -457,10 +472,10 @@ __global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockAr
       const unsigned slot = warp + 4 * i;
       const unsigned col = slot_col(bp.p, bp.q, slot, a.n);
       int bytes = 0;
-      const double *src = base;
+      const double *src = a.A;
       if (col != kNoCol && row < limit) {
         bytes = (row + 1 < limit) ? 16 : 8;
-        src = base + (size_t)col * ld + row;
+        src = col_ptr(a, isa, col) + row;
       }
       cp_async16(dst + slot * kTileStride, src, bytes);
     }
@@ -477,7 +492,7 @@ __global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockAr
   }
 
   double wf[8][4];
-  unsigned sc[4][2];
+  Pair cur_bp = {0u, 0u};
   unsigned cur_pair = 0xffffffffu;
   for (unsigned tau = t0; tau < t1; ++tau) {
     cp_async_wait<STAGES - 2>();
@@ -492,21 +507,15 @@ __global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockAr
     const unsigned pr = active[ap];
     if (pr != cur_pair) {  // new block pair: its W (B fragments) and the columns this lane stores to
       cur_pair = pr;
-      const Pair bp = sameh_pair(a.nb, k, pr);
+      const Pair bp = block_pair(a, k, pr);
       const double *w = wbuf + (size_t)pr * kD * kD;
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks)
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) wf[ks][nt] = w[(8 * nt + g) * kD + 4 * ks + tg];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        sc[nt][0] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg, a.n);
-        sc[nt][1] = slot_col(bp.p, bp.q, 8 * nt + 2 * tg + 1, a.n);
-      }
+      cur_bp = bp;
     }
     const bool isa = t < tpa;
-    double *base = isa ? a.A : a.V;
-    const size_t ld = isa ? a.lda : a.ldv;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row0 = (isa ? t : t - tpa) * kTileRows + 16 * warp;
     const double *tile = tiles + ((tau - t0) % STAGES) * kTileDoubles + 16 * warp + g;
@@ -526,8 +535,10 @@ __global__ void __launch_bounds__(128, 4) blk_update_staged_kernel(const BlockAr
       if (row < limit) {
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-          if (sc[nt][0] != kNoCol) base[(size_t)sc[nt][0] * ld + row] = d[nt][0];
-          if (sc[nt][1] != kNoCol) base[(size_t)sc[nt][1] * ld + row] = d[nt][1];
+          const unsigned c0 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg, a.n);
+          const unsigned c1 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg + 1, a.n);
+          if (c0 != kNoCol) col_ptr(a, isa, c0)[row] = d[nt][0];
+          if (c1 != kNoCol) col_ptr(a, isa, c1)[row] = d[nt][1];
         }
       }
     }
@@ -566,10 +577,19 @@ void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doub
   *flag_ints = pairs;
 }
 
-int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
+int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
                     unsigned long long *launches, const BlockProbe *probe) {
-  const unsigned pairs = a.nb / 2;
+  const unsigned pairs = a_in.nb / 2;
   if (pairs == 0) return SVDJ_OK;
+  BlockArgs a = a_in;
+  if (a.A2 == nullptr || a.split >= a.n) {  // single buffer
+    a.split = a.n;
+    a.A2 = a.A;
+    a.V2 = a.V;
+  } else {  // pre-bias the second buffers so that kernels index every column with its own number
+    a.A2 = a.A2 - (size_t)a.split * a.lda;
+    if (a.V2 != nullptr) a.V2 = a.V2 - (size_t)a.split * a.ldv;
+  }
   const unsigned splits = gram_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + 3u) & ~3u;  // k-steps are 4 rows
@@ -581,7 +601,9 @@ int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf,
   if (usplits > ucap) usplits = ucap;
   if (usplits < 1) usplits = 1;
   const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
-                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0)));
+                       ((reinterpret_cast<uintptr_t>(a.A2) & 15) == 0) &&
+                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0) &&
+                                        ((reinterpret_cast<uintptr_t>(a.V2) & 15) == 0)));
   if (aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update()) {
     static const int sm_count = [] {
       int dev = 0, n = 148;
@@ -593,7 +615,7 @@ int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf,
                                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     SVDJ_CUDA_TRY(attr);
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-    blk_update_staged_kernel<kUpdStages><<<sm_count * 4, 128, smem, st>>>(a, k, wbuf, wflag, pairs,
+    blk_update_staged_kernel<kUpdStages><<<sm_count * kUpdCtasPerSm, 128, smem, st>>>(a, k, wbuf, wflag, pairs,
                                                                           probe ? probe->active_pairs : nullptr);
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   } else {

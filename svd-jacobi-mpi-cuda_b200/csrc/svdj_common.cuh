@@ -171,6 +171,11 @@ struct BlockArgs {
   unsigned vrows;
   int rotate_v;
   unsigned nb;  // number of column blocks, ceil(n / 16)
+  // second buffers: column c >= split lives at A2 + (c - split) * lda (V2 likewise); split = n when unused
+  double *A2;
+  double *V2;
+  unsigned split;
+  int sched;  // 0: round-robin over all nb blocks; 1: bipartite, first half of the blocks against the second
   double tol;
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve

@@ -1,0 +1,126 @@
+// svdj_ring.cu -- entry points for drivers that spread the columns over several GPUs.
+//
+// The reference distributes the pairs of a step over MPI ranks through a star: rank 0 packs and sends
+// every rank its columns of A and V, receives them back and barriers, every step
+// (lib/JacobiMethods.cu:335-432, 607-694).  Here each rank (one process per GPU) keeps two column
+// blocks resident -- A-block m x w and V-block n x w each -- orthogonalises them against each other with
+// the block-Jacobi kernels, and passes blocks to its ring neighbours between phases (the driver is
+// svd-jacobi-mpi-cuda_b200/ring.py: torch.distributed / NCCL for the exchange, or peer stores fused into
+// the update kernel).  This file is the per-rank compute: a "phase" = all round-robin steps over the
+// blocks of the two buffers (SVDJ_PHASE_ALL: every pair of local columns; SVDJ_PHASE_CROSS: only pairs
+// with one column in each buffer).
+#include <cstring>
+#include <new>
+
+#include "svdj_common.cuh"
+
+namespace svdj {
+
+struct RingWorkspace {
+  size_t m = 0, ncols = 0;
+  double *gpart = nullptr;
+  double *wbuf = nullptr;
+  int *wflag = nullptr;
+  double *norms = nullptr;
+};
+
+static void ws_free(RingWorkspace *w) {
+  if (!w) return;
+  if (w->gpart) cudaFree(w->gpart);
+  if (w->wbuf) cudaFree(w->wbuf);
+  if (w->wflag) cudaFree(w->wflag);
+  if (w->norms) cudaFree(w->norms);
+  delete w;
+}
+
+}  // namespace svdj
+
+using namespace svdj;
+
+extern "C" {
+
+int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out) {
+  if (ws_out == nullptr) return -3;
+  *ws_out = nullptr;
+  if (m == 0 || m > 0x7fffffffu) return -1;
+  if (ncols_local == 0 || ncols_local % 32 != 0 || ncols_local > 0x7fffffffu) return -2;
+  RingWorkspace *w = new (std::nothrow) RingWorkspace();
+  if (!w) return SVDJ_ERR_ALLOC;
+  w->m = m;
+  w->ncols = ncols_local;
+  size_t gp = 0, wd = 0, fl = 0;
+  blk_scratch_sizes(m, ncols_local, &gp, &wd, &fl);
+  cudaError_t e = cudaMalloc(&w->gpart, sizeof(double) * gp);
+  if (e == cudaSuccess) e = cudaMalloc(&w->wbuf, sizeof(double) * wd);
+  if (e == cudaSuccess) e = cudaMalloc(&w->wflag, sizeof(int) * fl);
+  if (e == cudaSuccess) e = cudaMalloc(&w->norms, sizeof(double) * ncols_local);
+  if (e != cudaSuccess) {
+    set_error("svdj_ring_ws_create: cudaMalloc -> %s", cudaGetErrorString(e));
+    cudaGetLastError();
+    ws_free(w);
+    return SVDJ_ERR_ALLOC;
+  }
+  *ws_out = w;
+  return SVDJ_OK;
+}
+
+int svdj_ring_ws_destroy(void *ws) {
+  ws_free(static_cast<RingWorkspace *>(ws));
+  return SVDJ_OK;
+}
+
+int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
+                           double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
+                           int inner_sweeps, unsigned long long *d_counters, void *stream) {
+  RingWorkspace *W = static_cast<RingWorkspace *>(ws);
+  if (W == nullptr) return -1;
+  if (m == 0 || m != W->m) return -2;
+  if (w == 0 || w % 16 != 0 || 2 * w != W->ncols) return -4;
+  if (dA_left == nullptr || dA_right == nullptr) return -5;
+  if (lda < m) return -7;
+  if (rotate_v && (dV_left == nullptr || dV_right == nullptr)) return -8;
+  if (rotate_v && ldv < vrows) return -10;
+  if (phase != SVDJ_PHASE_ALL && phase != SVDJ_PHASE_CROSS) return -12;
+  BlockArgs b;
+  b.A = dA_left;
+  b.lda = lda;
+  b.V = dV_left;
+  b.ldv = ldv;
+  b.m = (unsigned)m;
+  b.n = (unsigned)(2 * w);
+  b.vrows = (unsigned)vrows;
+  b.rotate_v = rotate_v ? 1 : 0;
+  b.nb = blk_num_blocks(2 * w);
+  b.A2 = dA_right;
+  b.V2 = dV_right;
+  b.split = (unsigned)w;
+  b.sched = (phase == SVDJ_PHASE_CROSS) ? 1 : 0;
+  b.tol = tol;
+  b.threshold_mode = SVDJ_THRESH_REL;
+  b.max_inner_sweeps = inner_sweeps > 0 ? inner_sweeps : 2;
+  b.counters = reinterpret_cast<SweepCounters *>(d_counters);
+  const unsigned steps = (phase == SVDJ_PHASE_CROSS) ? b.nb / 2 : (unsigned)svdj_num_steps(b.nb);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (unsigned k = 1; k <= steps; ++k) {
+    if (int rc = blk_launch_step(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr)) return rc;
+  }
+  return SVDJ_OK;
+}
+
+int svdj_ring_finalize_device(void *ws, size_t m, size_t ncols, double *dA, size_t lda, double *d_sigma, int scale_u,
+                              void *stream) {
+  RingWorkspace *W = static_cast<RingWorkspace *>(ws);
+  if (W == nullptr) return -1;
+  if (ncols > W->ncols) return -3;
+  if (dA == nullptr) return -4;
+  if (lda < m) return -5;
+  if (d_sigma == nullptr) return -6;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int rc = launch_column_norms(dA, lda, m, ncols, d_sigma, st)) return rc;
+  if (scale_u) {
+    if (int rc = launch_gather_columns(dA, lda, dA, lda, m, ncols, nullptr, d_sigma, ncols, st)) return rc;
+  }
+  return SVDJ_OK;
+}
+
+}  // extern "C"

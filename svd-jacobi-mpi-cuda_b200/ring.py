@@ -1,0 +1,301 @@
+"""Multi-GPU driver: column blocks on a ring, one process per GPU.
+
+Replaces the reference's MPI star (``/root/reference/main.cu:583-942``: every round-robin step rank 0 packs
+and ``MPI_Send``s each rank its columns of A and V, ``MPI_Recv``s them back and barriers).  Here the n
+columns are cut into 2P column blocks of w = n/(2P) columns.  Rank r keeps two of them resident on its
+GPU (A-block m x w and the matching V-block n x w, packed in one allocation so that a block travels as
+one message).  A sweep is a round-robin tournament of the 2P blocks (circle method, 2P-1 rounds):
+
+    round 0      every rank orthogonalises ALL pairs of its 2w local columns  (SVDJ_PHASE_ALL)
+    rounds 1..   only the pairs across its two blocks                         (SVDJ_PHASE_CROSS)
+    after each round the blocks move one place round the ring (block 0 stays on rank 0): each rank
+    sends at most two blocks to its neighbours and receives at most two.
+
+so every pair of columns meets exactly once per sweep, as in the reference's ordering, and the only
+collective is one all-reduce of the rotation count per sweep (the reference barriers every step).
+Block moves are ``torch.distributed`` point-to-point operations batched per round (NCCL send/recv over
+NVLink on GPUs, gloo in the CPU tests); the per-rank compute is libsvdj's block-Jacobi phase
+(``svdj_ring_phase_device``).  The compute backend is injected so that the host logic (tournament,
+exchange, convergence) can be tested on CPU with a stand-in backend; the product backend is
+:class:`GpuBackend` and there is no CPU fallback in this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+PHASE_ALL, PHASE_CROSS = 0, 1
+
+
+# ----------------------------------------------------------------------------------------------------
+# tournament of the 2P column blocks (pure host logic)
+# ----------------------------------------------------------------------------------------------------
+def initial_arrangement(P: int) -> Tuple[List[int], List[int]]:
+    """Block ids held by rank r at round 0: top[r] = r, bottom[r] = P + r."""
+    return list(range(P)), list(range(P, 2 * P))
+
+
+def rotate(top: List[int], bottom: List[int]) -> Tuple[List[int], List[int]]:
+    """One move of the circle method: top[0] stays; the other 2P-1 places shift by one round the ring
+    top[1] -> top[2] -> ... -> top[P-1] -> bottom[P-1] -> ... -> bottom[0] -> top[1]."""
+    P = len(top)
+    if P == 1:
+        return list(top), list(bottom)
+    new_top = [top[0], bottom[0]] + top[1:P - 1]
+    new_bottom = bottom[1:] + [top[P - 1]]
+    return new_top, new_bottom
+
+
+def tournament_rounds(P: int) -> List[Tuple[List[int], List[int]]]:
+    """The 2P-1 arrangements of one sweep."""
+    top, bottom = initial_arrangement(P)
+    out = []
+    for _ in range(2 * P - 1):
+        out.append((list(top), list(bottom)))
+        top, bottom = rotate(top, bottom)
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------
+# compute backend on the GPU (the product path)
+# ----------------------------------------------------------------------------------------------------
+class GpuBackend:
+    """Per-rank compute through the C ABI of libsvdj.so (block-Jacobi phases on two resident column blocks)."""
+
+    def __init__(self, m: int, n: int, w: int, lda: int, ldv: int, tol: float, inner_sweeps: int = 0):
+        from . import lib, last_error, SvdjError  # the ctypes binding; fails loudly if libsvdj.so is missing
+
+        self.lib, self._last_error, self._err = lib, last_error, SvdjError
+        self.m, self.n, self.w, self.lda, self.ldv, self.tol, self.inner = m, n, w, lda, ldv, tol, inner_sweeps
+        ws = C.c_void_p()
+        rc = lib.svdj_ring_ws_create(m, 2 * w, C.byref(ws))
+        if rc != 0:
+            raise SvdjError(rc, last_error())
+        self.ws = ws
+
+    def close(self):
+        if self.ws:
+            self.lib.svdj_ring_ws_destroy(self.ws)
+            self.ws = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def phase(self, top, bottom, phase: int, counters: torch.Tensor) -> None:
+        """top/bottom: Block objects; counters: int64[2] on the device."""
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = self.lib.svdj_ring_phase_device(self.ws, self.m, self.n, self.w, top.A.data_ptr(), bottom.A.data_ptr(),
+                                             self.lda, top.V.data_ptr(), bottom.V.data_ptr(), self.ldv, 1, phase,
+                                             self.tol, self.inner, counters.data_ptr(), stream)
+        if rc != 0:
+            raise self._err(rc, self._last_error())
+
+    def finalize(self, blk, scale_u: bool = True) -> torch.Tensor:
+        sigma = torch.empty(self.w, dtype=torch.float64, device=blk.A.device)
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = self.lib.svdj_ring_finalize_device(self.ws, self.m, self.w, blk.A.data_ptr(), self.lda, sigma.data_ptr(),
+                                                1 if scale_u else 0, stream)
+        if rc != 0:
+            raise self._err(rc, self._last_error())
+        return sigma
+
+
+class Block:
+    """One column block: A-part (w columns of m rows) and V-part (w columns of n rows) in one allocation,
+    column-major (row j of the 2-D views is column j)."""
+
+    def __init__(self, w: int, m: int, n: int, lda: int, ldv: int, device):
+        self.buf = torch.zeros(w * (lda + ldv), dtype=torch.float64, device=device)
+        self.A = self.buf[: w * lda].view(w, lda)
+        self.V = self.buf[w * lda:].view(w, ldv)
+        self.block_id = -1
+
+
+# ----------------------------------------------------------------------------------------------------
+# the ring solver
+# ----------------------------------------------------------------------------------------------------
+class RingSolver:
+    def __init__(self, m: int, n: int, device, group=None, tol: Optional[float] = None, max_sweeps: int = 60,
+                 backend=None, inner_sweeps: int = 0):
+        self.group = group
+        self.P = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        P = self.P
+        if n % (2 * P) != 0 or (n // (2 * P)) % 16 != 0:
+            raise ValueError(f"n = {n} must be a multiple of 32 * world_size = {32 * P} (column blocks of 16)")
+        self.m, self.n, self.w = m, n, n // (2 * P)
+        self.lda = (m + 15) // 16 * 16   # 128-byte columns
+        self.ldv = (n + 15) // 16 * 16
+        self.device = device
+        self.tol = tol if tol is not None else m * 2.0 ** -53
+        self.max_sweeps = max_sweeps
+        self.backend = backend if backend is not None else GpuBackend(m, n, self.w, self.lda, self.ldv, self.tol,
+                                                                    inner_sweeps)
+        mk = lambda: Block(self.w, m, n, self.lda, self.ldv, device)  # noqa: E731
+        self.top, self.bottom = mk(), mk()
+        self.spare = [mk(), mk()]
+        t, b = initial_arrangement(P)
+        self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
+        self.counters = torch.zeros(2, dtype=torch.int64, device=device)
+        self.exchanged_bytes = 0
+
+    # -- data in ----------------------------------------------------------------------------------------
+    def fill_local(self, column_source: Callable[[int, int], torch.Tensor]) -> None:
+        """column_source(col0, count) -> (count, m) tensor with the columns [col0, col0+count) of A."""
+        for blk in (self.top, self.bottom):
+            c0 = blk.block_id * self.w
+            blk.A.zero_()
+            blk.A[:, : self.m].copy_(column_source(c0, self.w))
+            blk.V.zero_()
+            idx = torch.arange(self.w, device=self.device)
+            blk.V[idx, c0 + idx] = 1.0  # V = I (main.cu:462-474), this block's columns of it
+
+    def scatter_from_root(self, A_root: Optional[torch.Tensor]) -> None:
+        """Rank 0 holds A as an (n, m) tensor (column-major m x n); every rank receives its two blocks."""
+        if self.P == 1:
+            self.fill_local(lambda c0, cnt: A_root[c0:c0 + cnt])
+            return
+        ops, keep = [], []
+        if self.rank == 0:
+            t, b = initial_arrangement(self.P)
+            for r in range(1, self.P):
+                for bid in (t[r], b[r]):
+                    piece = A_root[bid * self.w:(bid + 1) * self.w].contiguous()
+                    keep.append(piece)
+                    ops.append(dist.P2POp(dist.isend, piece, r, self.group))
+            local = {0: A_root}
+        else:
+            recv = [torch.empty(self.w, self.m, dtype=torch.float64, device=self.device) for _ in range(2)]
+            for piece in recv:
+                ops.append(dist.P2POp(dist.irecv, piece, 0, self.group))
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        if self.rank == 0:
+            self.fill_local(lambda c0, cnt: A_root[c0:c0 + cnt])
+        else:
+            pieces = {self.top.block_id * self.w: recv[0], self.bottom.block_id * self.w: recv[1]}
+            self.fill_local(lambda c0, cnt: pieces[c0])
+
+    # -- one rotation of the blocks ---------------------------------------------------------------------
+    def _exchange(self) -> None:
+        P, r = self.P, self.rank
+        if P == 1:
+            return
+        sends, recvs = [], {}
+        # sends of the blocks held now (mirrors rotate())
+        if r == 0:
+            sends.append((self.bottom, 1))
+        else:
+            if r < P - 1:
+                sends.append((self.top, r + 1))
+            sends.append((self.bottom, r - 1))
+        # receives into spare blocks
+        spare = list(self.spare)
+        if r == 0:
+            recvs["bottom"] = (spare.pop(), 1)
+        else:
+            recvs["top"] = (spare.pop(), r - 1)
+            if r < P - 1:
+                recvs["bottom"] = (spare.pop(), r + 1)
+        ops = [dist.P2POp(dist.isend, blk.buf, peer, self.group) for blk, peer in sends]
+        ops += [dist.P2POp(dist.irecv, blk.buf, peer, self.group) for blk, peer in recvs.values()]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        self.exchanged_bytes += sum(blk.buf.numel() * 8 for blk, _ in sends)
+        # new arrangement: block ids follow rotate(); buffers are swapped, never copied
+        old_top = self.top
+        if r == 0:
+            new_top, new_bottom = old_top, recvs["bottom"][0]
+        elif r == P - 1:
+            new_top, new_bottom = recvs["top"][0], old_top  # the last rank's top turns the corner
+        else:
+            new_top, new_bottom = recvs["top"][0], recvs["bottom"][0]
+        everything = [self.top, self.bottom] + self.spare
+        self.top, self.bottom = new_top, new_bottom
+        self.spare = [b for b in everything if b is not new_top and b is not new_bottom]
+
+    def _set_ids(self, round_index: int) -> None:
+        t, b = self._arrangements[round_index % len(self._arrangements)]
+        self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
+
+    # -- the solve ---------------------------------------------------------------------------------------
+    def solve(self) -> dict:
+        self._arrangements = tournament_rounds(self.P)
+        rounds = len(self._arrangements)
+        sweeps, converged, applied_total, last_off = 0, False, 0, 0.0
+        for sweep in range(self.max_sweeps):
+            self.counters.zero_()
+            for rd in range(rounds):
+                self.backend.phase(self.top, self.bottom, PHASE_ALL if rd == 0 else PHASE_CROSS, self.counters)
+                self._exchange()
+                self._set_ids(rd + 1)
+            # one collective per sweep: rotations (sum) and largest off-diagonal cosine (max of the bit patterns)
+            if self.P > 1:
+                dist.all_reduce(self.counters[0:1], op=dist.ReduceOp.SUM, group=self.group)
+                dist.all_reduce(self.counters[1:2], op=dist.ReduceOp.MAX, group=self.group)
+            host = self.counters.cpu()
+            applied = int(host[0])
+            last_off = float(host[1:2].view(torch.float64)[0])
+            applied_total += applied
+            sweeps = sweep + 1
+            if applied == 0:
+                converged = True
+                break
+        return {"sweeps": sweeps, "converged": converged, "applied": applied_total, "last_offdiag": last_off,
+                "exchanged_bytes": self.exchanged_bytes}
+
+    # -- data out ----------------------------------------------------------------------------------------
+    def finalize(self, scale_u: bool = True):
+        """sigma of the local columns (and U = A / sigma in place).  Returns (sigma_all_sorted, order) where
+        order[k] = global position (block_id * w + j) of the k-th largest singular value; both on every rank."""
+        s_top = self.backend.finalize(self.top, scale_u)
+        s_bot = self.backend.finalize(self.bottom, scale_u)
+        local = torch.cat([s_top, s_bot])
+        ids = torch.cat([self.top.block_id * self.w + torch.arange(self.w, device=self.device),
+                         self.bottom.block_id * self.w + torch.arange(self.w, device=self.device)])
+        if self.P > 1:
+            all_s = [torch.empty_like(local) for _ in range(self.P)]
+            all_i = [torch.empty_like(ids) for _ in range(self.P)]
+            dist.all_gather(all_s, local, group=self.group)
+            dist.all_gather(all_i, ids, group=self.group)
+            local, ids = torch.cat(all_s), torch.cat(all_i)
+        order = torch.argsort(local, descending=True, stable=True)
+        return local[order], ids[order]
+
+    def gather_to_root(self, order_ids: torch.Tensor):
+        """Rank 0 receives every block and returns (U, V) as (n, m) and (n, n) tensors whose row k is the column
+        of the k-th largest singular value; other ranks return (None, None)."""
+        n, m, w = self.n, self.m, self.w
+        if self.rank == 0:
+            U_all = torch.empty(n, self.lda, dtype=torch.float64, device=self.device)
+            V_all = torch.empty(n, self.ldv, dtype=torch.float64, device=self.device)
+        ops = []
+        if self.P > 1:
+            # everyone tells rank 0 which blocks it holds (ids changed during the tournament)
+            mine = torch.tensor([self.top.block_id, self.bottom.block_id], dtype=torch.int64, device=self.device)
+            held = [torch.empty_like(mine) for _ in range(self.P)]
+            dist.all_gather(held, mine, group=self.group)
+            if self.rank == 0:
+                for r in range(1, self.P):
+                    for slot in range(2):
+                        bid = int(held[r][slot])
+                        ops.append(dist.P2POp(dist.irecv, U_all[bid * w:(bid + 1) * w], r, self.group))
+                        ops.append(dist.P2POp(dist.irecv, V_all[bid * w:(bid + 1) * w], r, self.group))
+            else:
+                for blk in (self.top, self.bottom):
+                    ops.append(dist.P2POp(dist.isend, blk.A, 0, self.group))
+                    ops.append(dist.P2POp(dist.isend, blk.V, 0, self.group))
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        if self.rank != 0:
+            return None, None
+        for blk in (self.top, self.bottom):
+            U_all[blk.block_id * w:(blk.block_id + 1) * w].copy_(blk.A)
+            V_all[blk.block_id * w:(blk.block_id + 1) * w].copy_(blk.V)
+        return U_all[order_ids, :m], V_all[order_ids, :n]

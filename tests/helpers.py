@@ -188,3 +188,12 @@ def fix_signs(U, V):
     V *= sg
     U[:, : V.shape[1]] *= sg[: U.shape[1]] if U.shape[1] <= V.shape[1] else np.pad(sg, (0, U.shape[1] - len(sg)), constant_values=1.0)
     return U, V
+
+
+def uniform_columns(m: int, n: int, seed: int, c0: int, count: int) -> np.ndarray:
+    """Columns [c0, c0+count) of uniform_matrix(m, n, seed) as a (count, m) array (row j = column c0+j),
+    without building the whole matrix: every rank of a multi-GPU run generates its own columns."""
+    with np.errstate(over="ignore"):
+        idx = (np.arange(count * m, dtype=np.uint64) + np.uint64(c0 * m)) + np.uint64(seed) * np.uint64(0x100000001B3)
+        bits = _splitmix64(idx)
+    return ((bits >> np.uint64(11)).astype(np.float64) * 2.0 ** -53).reshape(count, m)

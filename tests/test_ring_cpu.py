@@ -1,0 +1,154 @@
+"""CPU tests of the multi-GPU host logic (svd-jacobi-mpi-cuda_b200/ring.py) with gloo, world_size 2 and 3.
+
+The product's per-rank compute is libsvdj's GPU phase; here a numpy stand-in backend (test-only, the oracle's
+formulas: lib/JacobiMethods.cu:450-477, 1483-1491) takes its place so that the tournament of column blocks,
+the block exchange, the per-sweep all-reduce and the scatter/gather can be checked without a GPU.
+"""
+import importlib
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import helpers as H
+
+
+def _ring():
+    return importlib.import_module("svd-jacobi-mpi-cuda_b200.ring")
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 5, 8])
+def test_tournament_meets_every_block_pair_exactly_once(P):
+    ring = _ring()
+    rounds = ring.tournament_rounds(P)
+    assert len(rounds) == 2 * P - 1
+    seen = set()
+    for top, bottom in rounds:
+        assert sorted(top + bottom) == list(range(2 * P)), "every block is held by exactly one rank"
+        assert top[0] == 0, "block 0 never moves"
+        for x, y in zip(top, bottom):
+            key = (min(x, y), max(x, y))
+            assert key not in seen
+            seen.add(key)
+    assert len(seen) == P * (2 * P - 1)
+    # the rotation has period 2P-1: a sweep ends in the arrangement it started from
+    t, b = ring.initial_arrangement(P)
+    for _ in range(2 * P - 1):
+        t, b = ring.rotate(t, b)
+    assert (t, b) == ring.initial_arrangement(P)
+
+
+class NumpyBackend:
+    """Stand-in for GpuBackend: same interface, level-1 rotations in numpy on CPU tensors."""
+
+    def __init__(self, m, n, w, tol):
+        self.m, self.n, self.w, self.tol = m, n, w, tol
+
+    def phase(self, top, bottom, phase, counters):
+        m, n, w = self.m, self.n, self.w
+        A = [top.A.numpy(), bottom.A.numpy()]
+        V = [top.V.numpy(), bottom.V.numpy()]
+
+        def col(c):
+            return (A[c // w][c % w, :m], V[c // w][c % w, :n])
+
+        if phase == 0:
+            steps = [H.oracle_schedule(2 * w, st) for st in range(H.oracle_lib().oracle_num_steps(2 * w))]
+        else:
+            steps = [np.array([(i, w + (i + t) % w) for i in range(w)]) for t in range(w)]
+        applied, mx = 0, 0.0
+        for pairs in steps:
+            for p, q in pairs:
+                ap, vp = col(int(p))
+                aq, vq = col(int(q))
+                alpha, beta, gamma = float(ap @ aq), float(ap @ ap), float(aq @ aq)
+                den = np.sqrt(beta * gamma)
+                if den > 0:
+                    mx = max(mx, abs(alpha) / den)
+                if not abs(alpha) > self.tol * den:
+                    continue
+                tau = (gamma - beta) / (2.0 * alpha)
+                t = 1.0 / (tau + np.sqrt(1 + tau * tau)) if tau >= 0 else 1.0 / (tau - np.sqrt(1 + tau * tau))
+                c = 1.0 / np.sqrt(1 + t * t)
+                s = t * c
+                for x, y in ((ap, aq), (vp, vq)):
+                    tmp = x.copy()
+                    x[:] = c * tmp - s * y
+                    y[:] = s * tmp + c * y
+                applied += 1
+        counters[0] += applied
+        bits = int(np.array([mx]).view(np.int64)[0])
+        counters[1] = max(int(counters[1]), bits)
+
+    def finalize(self, blk, scale_u=True):
+        a = blk.A.numpy()[:, : self.m]
+        sigma = np.linalg.norm(a, axis=1)
+        if scale_u:
+            nz = sigma > 0
+            a[nz] /= sigma[nz, None]
+        return torch.from_numpy(sigma.copy())
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, m, n, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ring = _ring()
+        A0 = H.uniform_matrix(m, n, seed=m + n)
+        w = n // (2 * world)
+        solver = ring.RingSolver(m, n, torch.device("cpu"), backend=NumpyBackend(m, n, w, m * 2.0 ** -53))
+        # rank 0 owns the matrix (the reference's contract: only the root's A, s, V are valid, main.cu:1455)
+        A_root = torch.from_numpy(np.ascontiguousarray(A0.T)) if rank == 0 else None
+        solver.scatter_from_root(A_root)
+        # every rank must have received exactly its two blocks
+        for blk in (solver.top, solver.bottom):
+            c0 = blk.block_id * w
+            assert np.array_equal(blk.A.numpy()[:, :m], A0.T[c0:c0 + w])
+        # the physical exchange follows the tournament table: stamp, rotate a whole sweep, compare
+        arrangements = ring.tournament_rounds(world)
+        solver._arrangements = arrangements
+        for rd in range(len(arrangements)):
+            t, b = arrangements[rd]
+            assert solver.top.block_id == t[rank] and solver.bottom.block_id == b[rank]
+            assert np.array_equal(solver.top.A.numpy()[:, :m], A0.T[t[rank] * w:(t[rank] + 1) * w])
+            assert np.array_equal(solver.bottom.A.numpy()[:, :m], A0.T[b[rank] * w:(b[rank] + 1) * w])
+            solver._exchange()
+            solver._set_ids(rd + 1)
+        stats = solver.solve()
+        assert stats["converged"], stats
+        sigma, order = solver.finalize()
+        U, V = solver.gather_to_root(order)
+        if rank == 0:
+            np.savez(out_path, U=U.numpy().T, s=sigma.numpy(), V=V.numpy().T, sweeps=stats["sweeps"],
+                     exchanged=stats["exchanged_bytes"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,m,n", [(2, 80, 64), (3, 100, 96)])
+def test_ring_solver_with_gloo(tmp_path, world, m, n):
+    out = str(tmp_path / "result.npz")
+    mp.spawn(_worker, args=(world, _free_port(), m, n, out), nprocs=world, join=True)
+    r = np.load(out)
+    A0 = H.uniform_matrix(m, n, seed=m + n)
+    U, s, V = r["U"], r["s"], r["V"]
+    assert np.all(np.diff(s) <= 0)
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(A0, U, s, V)
+    bound = 10 * max(m, n) * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+    assert int(r["sweeps"]) <= 20 and int(r["exchanged"]) > 0
+    # same singular values as the single-process oracle
+    Uo, so, Vo, ost, rc = H.oracle_svd(A0)
+    assert H.sigma_error_normwise(s, so) <= 1e-12
