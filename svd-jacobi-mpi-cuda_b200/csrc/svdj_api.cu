@@ -202,6 +202,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   b.V2 = nullptr;
   b.split = (unsigned)n;
   b.sched = 0;
+  b.sort_cols = 1;
   b.tol = o.tol;
   b.threshold_mode = o.threshold_mode;
   // Two cyclic sweeps of the 32 x 32 eigen-solve per visit: measured to need as few outer sweeps as a fully

@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
       const Pair bp = block_pair(a, k, pair);
       const unsigned vmask = __ballot_sync(0xffffffffu, slot_col(bp.p, bp.q, tid, a.n) != kNoCol);
       int out = tid;
-      if ((vmask >> tid) & 1u) {
+      if (a.sort_cols && ((vmask >> tid) & 1u)) {
         const double di = Gb[cur][tid][tid];
         int rk = 0;
         for (int j = 0; j < kD; ++j) {

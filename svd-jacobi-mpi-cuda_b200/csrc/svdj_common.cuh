@@ -176,6 +176,10 @@ struct BlockArgs {
   double *V2;
   unsigned split;
   int sched;  // 0: round-robin over all nb blocks; 1: bipartite, first half of the blocks against the second
+  // 1: order the 32 columns of a block pair by decreasing eigenvalue (fewer sweeps on one GPU).  Ring drivers
+  // pass 0: the ordering moves columns from one travelling block to the other, and with the tournament's
+  // fixed block 0 the largest column of the last rank then never meets the largest column of rank 0.
+  int sort_cols;
   double tol;
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve

@@ -95,6 +95,7 @@ int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *d
   b.V2 = dV_right;
   b.split = (unsigned)w;
   b.sched = (phase == SVDJ_PHASE_CROSS) ? 1 : 0;
+  b.sort_cols = 0;
   b.tol = tol;
   b.threshold_mode = SVDJ_THRESH_REL;
   b.max_inner_sweeps = inner_sweeps > 0 ? inner_sweeps : 2;

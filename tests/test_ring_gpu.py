@@ -47,7 +47,7 @@ def test_emulated_tournament_on_one_gpu(P):
     """All P ranks' blocks live on one GPU and the rounds run rank after rank: checks SVDJ_PHASE_CROSS (bipartite
     schedule, two buffers) and that the tournament orthogonalises every pair of columns."""
     ring = _ring()
-    m, n = 200, 64 * P
+    m, n = 64 * P + 40, 64 * P
     w = n // (2 * P)
     A0 = H.uniform_matrix(m, n, seed=P)
     dev = torch.device("cuda", 0)
