@@ -205,6 +205,103 @@ def run_reference(args):
     return 0
 
 
+def run_ring(args, svdj, world, rank, local_rank):
+    """N > 1: the same n x n solve spread over N GPUs (strong scaling): 2N column blocks on a ring, NCCL send/recv
+    between rounds, one all-reduce per sweep (svd-jacobi-mpi-cuda_b200/ring.py)."""
+    import torch
+    import torch.distributed as dist
+
+    import helpers as H
+
+    ring = importlib.import_module("svd-jacobi-mpi-cuda_b200.ring")
+    n = m = args.n
+    dev = torch.device("cuda", local_rank)
+    solver = ring.RingSolver(m, n, dev)
+    w = solver.w
+
+    # every rank generates its own columns (counter-based generator: same matrix as the 1-GPU run)
+    init = {}
+    for blk in (solver.top, solver.bottom):
+        init[blk.block_id * w] = torch.from_numpy(H.uniform_columns(m, n, n, blk.block_id * w, w)).to(dev)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_solve():
+        solver.fill_local(lambda c0, cnt: init[c0])
+        st = solver.solve()
+        sigma, order = solver.finalize()
+        return st, sigma, order
+
+    for _ in range(args.warmup):
+        one_solve()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    solver.exchanged_bytes = 0
+    solver.backend.launches = 0
+    ev0.record()
+    for _ in range(args.steps):
+        st, sigma, order = one_solve()
+    ev1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ev0.elapsed_time(ev1) * 1e-3], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    per_step_s = float(t.item()) / args.steps
+    sent_per_solve = solver.exchanged_bytes / args.steps
+    launches = torch.tensor([solver.backend.launches], dtype=torch.int64, device=dev)
+    dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+
+    # e2e: the matrix starts in rank 0's pinned host memory and U, s, V end there (the reference's contract: only
+    # the root holds A, s, V -- main.cu:1455, 1548-1556)
+    hA0 = torch.from_numpy(np.ascontiguousarray(H.uniform_matrix(m, n, seed=n).T)).pin_memory() if rank == 0 else None
+    e2e = []
+    for it in range(1 + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        solver.scatter_from_root(hA0.to(dev, non_blocking=True) if rank == 0 else None)
+        st, sigma, order = solver.solve(), None, None
+        sigma, order = solver.finalize()
+        U, V = solver.gather_to_root(order)
+        if rank == 0:
+            hU, hV, hs = U.cpu(), V.cpu(), sigma.cpu()
+        barrier()
+        if it > 0:
+            e2e.append(time.perf_counter() - t0)
+    e2e_s = float(np.mean(e2e))
+
+    if rank == 0:
+        Ud, Vd, Sd = hU.to(dev).T, hV.to(dev).T, hs.to(dev)
+        A0d = hA0.to(dev).T
+        eye = torch.eye(n, dtype=torch.float64, device=dev)
+        acc = {"orth_u": float((Ud.T @ Ud - eye).abs().max()), "orth_v": float((Vd.T @ Vd - eye).abs().max()),
+               "resid": float(torch.linalg.norm(A0d - (Ud * Sd) @ Vd.T) / torch.linalg.norm(A0d)),
+               "bound_10_n_eps": 10 * n * 2.0 ** -52}
+        line = {
+            "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence",
+                       "variant": "block", "tol": "m*2^-53 relative",
+                       "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20),
+                       "parallelism": f"{2 * world} column blocks of {w} columns on a ring of {world} GPUs "
+                                      "(NCCL send/recv between rounds, 1 all-reduce per sweep)"},
+            "sweeps": st["sweeps"], "rotations_applied": st["applied"],
+            "ring": {"bytes_sent_per_rank_per_solve": sent_per_solve, "rounds_per_sweep": 2 * world - 1},
+            "roofline": None, "cpu_baseline": None,
+            "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
+                    "d2h_bytes_per_step": (m * n + n * n + n) * 8},
+            "gpu_launches": int(launches.item()), "clocks": clocks, "accuracy": acc,
+        }
+        print(json.dumps(line))
+    dist.destroy_process_group()
+    return 0
+
+
 def run_svdj(args):
     import torch
     import torch.distributed as dist
@@ -219,6 +316,9 @@ def run_svdj(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    if world > 1:
+        return run_ring(args, svdj, world, rank, local_rank)
 
     n = m = args.n
     A0 = H.uniform_matrix(m, n, seed=n)

@@ -75,6 +75,7 @@ class GpuBackend:
         if rc != 0:
             raise SvdjError(rc, last_error())
         self.ws = ws
+        self.launches = 0  # kernels launched through this backend (3 per block step, 1-2 per finalize)
 
     def close(self):
         if self.ws:
@@ -95,6 +96,8 @@ class GpuBackend:
                                              self.tol, self.inner, counters.data_ptr(), stream)
         if rc != 0:
             raise self._err(rc, self._last_error())
+        nb = 2 * self.w // 16
+        self.launches += 3 * (nb // 2 if phase == PHASE_CROSS else int(self.lib.svdj_num_steps(nb)))
 
     def finalize(self, blk, scale_u: bool = True) -> torch.Tensor:
         sigma = torch.empty(self.w, dtype=torch.float64, device=blk.A.device)
@@ -103,6 +106,7 @@ class GpuBackend:
                                                 1 if scale_u else 0, stream)
         if rc != 0:
             raise self._err(rc, self._last_error())
+        self.launches += 2 if scale_u else 1
         return sigma
 
 
