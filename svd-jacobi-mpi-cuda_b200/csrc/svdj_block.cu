@@ -156,9 +156,12 @@ __device__ __forceinline__ void fast_rotation(double alpha, double beta, double 
   const double zeta = gamma - beta;
   const double a2 = 2.0 * alpha;
   // scale to avoid under/overflow of the squares (Gram entries span the square of the column norms' range)
+  // (a power of two built from the exponent bits of the larger magnitude: a handful of integer instructions
+  // where ilogb/scalbn cost ~60 with branches, on the critical path of every step)
   const double big = fmax(fabs(zeta), fabs(a2));
-  const int e = ilogb(big);
-  const double z = scalbn(zeta, -e), y = scalbn(a2, -e);
+  const int ex = (__double2hiint(big) >> 20) & 0x7ff;
+  const double scale = __hiloint2double((2046 - ex) << 20, 0);  // 2^(1023 - ex): max(|z|, |y|) lands in [1, 2)
+  const double z = zeta * scale, y = a2 * scale;
   const double rh = rsqrt(z * z + y * y);
   const double cc = 0.5 + 0.5 * fabs(z) * rh;
   const double rcc = rsqrt(cc);
@@ -220,20 +223,22 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
   for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
     int sweep_rot = 0;
     for (int t = 0; t < kD - 1; ++t) {
-      // the step's 16 rotations, computed by every warp (lane & 15 = pair index)
-      int p2, q2;
+      // the step's 16 rotations, computed by every warp (lane & 15 = pair index).  All eleven shared-memory
+      // loads of the step are issued before the rotation arithmetic so that their latency hides behind it.
+      int p2, q2, p1, q1;
       circle_pair(t, j2, p2, q2);
+      circle_pair(t, j1, p1, q1);
       const double al = Gb[cur][p2][q2], be = Gb[cur][p2][p2], ga = Gb[cur][q2][q2];
+      const double g11 = Gb[cur][p1][p2], g12 = Gb[cur][p1][q2], g21 = Gb[cur][q1][p2], g22 = Gb[cur][q1][q2];
+      const double wp0 = W[j1][p2], wq0 = W[j1][q2], wp1 = W[j1 + 16][p2], wq1 = W[j1 + 16][q2];
       const bool rot = al * al > tol2 * be * ga;  // |alpha| > tol sqrt(beta gamma), lib/JacobiMethods.cu:462/466
       double c2 = 1.0, s2 = 0.0;
       if (rot) fast_rotation(al, be, ga, c2, s2);
       const unsigned mask = __ballot_sync(0xffffffffu, rot) & 0xffffu;
       if (mask == 0u) continue;  // every warp sees the same 16 decisions: uniform across the CTA
       sweep_rot += __popc(mask);
-      const int p1 = __shfl_sync(0xffffffffu, p2, j1), q1 = __shfl_sync(0xffffffffu, q2, j1);
       const double c1 = __shfl_sync(0xffffffffu, c2, j1), s1 = __shfl_sync(0xffffffffu, s2, j1);
       {
-        const double g11 = Gb[cur][p1][p2], g12 = Gb[cur][p1][q2], g21 = Gb[cur][q1][p2], g22 = Gb[cur][q1][q2];
         // columns: col_p' = c col_p - s col_q, col_q' = s col_p + c col_q (the kernel at :1483-1491)
         const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
         const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
@@ -248,13 +253,10 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
         Gb[cur ^ 1][p1][q2] = n12;
         Gb[cur ^ 1][q1][p2] = n21;
         Gb[cur ^ 1][q1][q2] = n22;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int r = j1 + 16 * i;  // rows r of W, pair j2
-          const double wp = W[r][p2], wq = W[r][q2];
-          W[r][p2] = c2 * wp - s2 * wq;
-          W[r][q2] = s2 * wp + c2 * wq;
-        }
+        W[j1][p2] = c2 * wp0 - s2 * wq0;  // rows j1 and j1 + 16 of W, pair j2
+        W[j1][q2] = s2 * wp0 + c2 * wq0;
+        W[j1 + 16][p2] = c2 * wp1 - s2 * wq1;
+        W[j1 + 16][q2] = s2 * wp1 + c2 * wq1;
       }
       cur ^= 1;
       __syncthreads();
@@ -329,7 +331,13 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
 template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs a, const unsigned k,
                                                                 const double *__restrict__ wbuf,
-                                                                const int *__restrict__ wflag) {
+                                                                const int *__restrict__ wflag,
+                                                                unsigned long long *__restrict__ active_out) {
+  if (active_out != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+    unsigned cnt = 0;
+    for (unsigned p = 0; p < gridDim.x; ++p) cnt += wflag[p] != 0;
+    *active_out += cnt;
+  }
   if (!wflag[blockIdx.x]) return;  // nothing was rotated in this block pair: W = I
   const Pair bp = block_pair(a, k, blockIdx.x);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -547,6 +555,100 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
 }
 
 // ------------------------------------------------------------------------------------------------
+// K1, staged: the same partial Gram matrices for aligned layouts.  grid (block pairs, row splits) as
+// above, but the 64-row x 32-column tiles of a CTA's row range come in through the 3-stage cp.async
+// pipeline of the update kernel (512 contiguous bytes per warp-level copy) instead of 8-byte fragment
+// loads straight from global memory, which left the plain kernel at half of the HBM rate.
+// ------------------------------------------------------------------------------------------------
+template <int STAGES>
+__global__ void __launch_bounds__(128) blk_gram_staged_kernel(const BlockArgs a, const unsigned k,
+                                                              const unsigned rows_per_split,
+                                                              double *__restrict__ gpart) {
+  extern __shared__ __align__(16) double tiles[];  // STAGES x 32 columns x kTileStride; reused for the reduction
+  const Pair bp = block_pair(a, k, blockIdx.x);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+  const unsigned r0 = blockIdx.y * rows_per_split;  // a multiple of 64
+  const unsigned r1 = min(a.m, r0 + rows_per_split);
+  const unsigned ntiles = r0 < r1 ? (r1 - r0 + kTileRows - 1) / kTileRows : 0;
+
+  const double *cptr[8];  // this thread copies column slots warp + 4 i
+  bool cval[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const unsigned c = slot_col(bp.p, bp.q, warp + 4 * i, a.n);
+    cval[i] = (c != kNoCol);
+    cptr[i] = col_ptr(a, true, cval[i] ? c : 0);
+  }
+  auto issue_tile = [&](unsigned t, int stage) {
+    const unsigned row = r0 + t * kTileRows + 2 * lane;
+    double *dst = tiles + stage * kTileDoubles + 2 * lane;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int bytes = 0;
+      const double *src = a.A;
+      if (cval[i] && row < r1) {
+        bytes = (row + 1 < r1) ? 16 : 8;
+        src = cptr[i] + row;
+      }
+      cp_async16(dst + (warp + 4 * i) * kTileStride, src, bytes);
+    }
+  };
+
+  unsigned issued = 0;
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (issued < ntiles) {
+      issue_tile(issued, s);
+      ++issued;
+    }
+    cp_async_commit();
+  }
+  double acc[kGramTiles][2];
+#pragma unroll
+  for (int t = 0; t < kGramTiles; ++t) acc[t][0] = acc[t][1] = 0.0;
+
+  for (unsigned t = 0; t < ntiles; ++t) {
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();
+    if (issued < ntiles) {
+      issue_tile(issued, (int)(issued % STAGES));
+      ++issued;
+    }
+    cp_async_commit();
+    // rows 16 warp .. 16 warp + 15 of the tile: four k-steps of 4 rows; rows past r1 were zero-filled
+    const double *tile = tiles + (t % STAGES) * kTileDoubles + 16 * warp + tg;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      double f[4];
+#pragma unroll
+      for (int gi = 0; gi < 4; ++gi) f[gi] = tile[(8 * gi + g) * kTileStride + 4 * ks];
+      int tt = 0;
+#pragma unroll
+      for (int ti = 0; ti < 4; ++ti)
+#pragma unroll
+        for (int tj = ti; tj < 4; ++tj) {
+          dmma884(acc[tt][0], acc[tt][1], f[ti], f[tj]);
+          ++tt;
+        }
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();  // the tile buffers become the reduction buffer
+  double *red = tiles;  // [4 warps][kGramPart]
+#pragma unroll
+  for (int t = 0; t < kGramTiles; ++t) {
+    red[warp * kGramPart + t * 64 + lane * 2 + 0] = acc[t][0];
+    red[warp * kGramPart + t * 64 + lane * 2 + 1] = acc[t][1];
+  }
+  __syncthreads();
+  double *dst = gpart + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * kGramPart;
+  for (unsigned i = threadIdx.x; i < kGramPart; i += 128) {
+    dst[i] = red[i] + red[kGramPart + i] + red[2 * kGramPart + i] + red[3 * kGramPart + i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 static constexpr int kGramWarps = 4, kGramUnroll = 4, kUpdWarps = 4;
@@ -593,24 +695,34 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
   const unsigned splits = gram_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + 3u) & ~3u;  // k-steps are 4 rows
-  blk_gram_kernel<kGramWarps, kGramUnroll><<<dim3(pairs, splits), kGramWarps * 32, 0, st>>>(a, k, rps, gpart);
+  const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(a.A2) & 15) == 0) &&
+                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0) &&
+                                        ((reinterpret_cast<uintptr_t>(a.V2) & 15) == 0)));
+  const bool staged = aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update();
+  constexpr size_t kStageSmem = sizeof(double) * kUpdStages * kTileDoubles;
+  if (staged) {
+    static const cudaError_t gattr = cudaFuncSetAttribute(blk_gram_staged_kernel<kUpdStages>,
+                                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStageSmem);
+    SVDJ_CUDA_TRY(gattr);
+    rps = (rps + kTileRows - 1) / kTileRows * kTileRows;  // whole tiles per split
+    blk_gram_staged_kernel<kUpdStages><<<dim3(pairs, splits), 128, kStageSmem, st>>>(a, k, rps, gpart);
+  } else {
+    blk_gram_kernel<kGramWarps, kGramUnroll><<<dim3(pairs, splits), kGramWarps * 32, 0, st>>>(a, k, rps, gpart);
+  }
   blk_eig_kernel<<<pairs, 256, 0, st>>>(a, k, splits, gpart, wbuf, wflag);
   const unsigned strips = ((a.m + 7) >> 3) + (a.rotate_v ? ((a.vrows + 7) >> 3) : 0);
   unsigned usplits = (8 * 148 + pairs - 1) / pairs;
   const unsigned ucap = (strips + kUpdWarps * 4 - 1) / (kUpdWarps * 4);  // >= 4 strips per warp
   if (usplits > ucap) usplits = ucap;
   if (usplits < 1) usplits = 1;
-  const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
-                       ((reinterpret_cast<uintptr_t>(a.A2) & 15) == 0) &&
-                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0) &&
-                                        ((reinterpret_cast<uintptr_t>(a.V2) & 15) == 0)));
-  if (aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update()) {
+  if (staged) {
     static const int sm_count = [] {
       int dev = 0, n = 148;
       if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
       return n;
     }();
-    constexpr size_t smem = sizeof(double) * kUpdStages * kTileDoubles;
+    constexpr size_t smem = kStageSmem;
     static const cudaError_t attr = cudaFuncSetAttribute(blk_update_staged_kernel<kUpdStages>,
                                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     SVDJ_CUDA_TRY(attr);
@@ -619,7 +731,10 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
                                                                           probe ? probe->active_pairs : nullptr);
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   } else {
-    blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag);
+    if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
+    blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag,
+                                                                                  probe ? probe->active_pairs : nullptr);
+    if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   }
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());

@@ -131,3 +131,30 @@ def test_block_full_size_4096_properties(svdj):
     assert float((U.T @ U - eye).abs().max()) <= bound
     assert float((V.T @ V - eye).abs().max()) <= bound
     assert float(torch.linalg.norm(dA0.T - (U * ds) @ V.T) / torch.linalg.norm(dA0)) <= bound
+
+
+def test_unstaged_kernels_give_the_same_answer(svdj, monkeypatch):
+    """SVDJ_BLOCK_PLAIN=1 forces the fragment-from-global kernels (the fallback for unaligned layouts)."""
+    A0 = H.uniform_matrix(300, 200, seed=31)
+    A1, s1, V1, st1 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    monkeypatch.setenv("SVDJ_BLOCK_PLAIN", "1")
+    A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    monkeypatch.delenv("SVDJ_BLOCK_PLAIN")
+    assert st1.converged == 1 and st2.converged == 1
+    assert H.sigma_error_normwise(s2, s1) <= 1e-13
+    q = H.svd_quality(A0, A2, s2, V2)
+    assert max(q.values()) <= 10 * 300 * H.EPS
+    # an odd leading dimension on the device entry point takes the same fallback by itself
+    torch_ = torch
+    m, n, lda = 129, 96, 131
+    B0 = H.uniform_matrix(m, n, seed=32)
+    buf = torch_.zeros(n, lda, dtype=torch_.float64, device="cuda")
+    buf[:, :m] = torch_.from_numpy(np.ascontiguousarray(B0.T)).cuda()
+    ds = torch_.zeros(n, dtype=torch_.float64, device="cuda")
+    dV = torch_.zeros(n, n + 1, dtype=torch_.float64, device="cuda")
+    st = svdj.dgesvd_device(0, 0, m, n, buf.data_ptr(), lda, ds.data_ptr(), dV.data_ptr(), n + 1,
+                            svdj.default_opts(variant=svdj.VARIANT_BLOCK))
+    assert st.converged == 1
+    assert H.sigma_error_normwise(ds.cpu().numpy(), np.linalg.svd(B0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(B0, buf[:, :m].cpu().numpy().T, ds.cpu().numpy(), dV[:, :n].cpu().numpy().T)
+    assert max(q.values()) <= 10 * m * H.EPS
