@@ -158,3 +158,19 @@ def test_unstaged_kernels_give_the_same_answer(svdj, monkeypatch):
     assert H.sigma_error_normwise(ds.cpu().numpy(), np.linalg.svd(B0, compute_uv=False)) <= 1e-12
     q = H.svd_quality(B0, buf[:, :m].cpu().numpy().T, ds.cpu().numpy(), dV[:, :n].cpu().numpy().T)
     assert max(q.values()) <= 10 * m * H.EPS
+
+
+@pytest.mark.parametrize("qr_steps", [1, 2])
+def test_qr_preconditioned_front_end(svdj, qr_steps):
+    """Optional front-end (library QR + our Jacobi on R^T): graded spectrum, cond 1e12."""
+    import importlib
+    pre = importlib.import_module("svd-jacobi-mpi-cuda_b200.precond")
+    n = 512
+    A0, sigma = H.prescribed_spectrum(n, 1e12, seed=9)
+    A = torch.from_numpy(np.ascontiguousarray(A0)).cuda()
+    U, s, V, st = pre.dgesvd_preconditioned(A, svdj.default_opts(max_sweeps=60), qr_steps=qr_steps)
+    assert st.converged == 1 and st.sweeps <= 16, st.sweeps   # 47 sweeps without the QR step
+    U, s, V = U.cpu().numpy(), s.cpu().numpy(), V.cpu().numpy()
+    assert H.sigma_error_normwise(s, np.sort(sigma)[::-1]) <= 1e-12
+    q = H.svd_quality(A0, U, s, V)
+    assert max(q.values()) <= 10 * n * H.EPS, q
