@@ -463,7 +463,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="svdj", choices=["svdj", "reference"])
-    ap.add_argument("--n", type=int, default=4096)
+    ap.add_argument("--size", "--n", dest="n", type=int, default=4096)
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

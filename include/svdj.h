@@ -181,6 +181,27 @@ int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *d
 int svdj_ring_finalize_device(void *ws, size_t m, size_t ncols, double *dA, size_t lda, double *d_sigma,
                               int scale_u, void *stream);
 
+/*
+ * The block exchange fused into the update kernel.  In the reference the columns a rank has rotated
+ * go back to rank 0 by MPI_Send from host memory and are re-packed and re-sent before the next step
+ * (main.cu:852-942).  svdj_ring_phase_send_device is svdj_ring_phase_device whose LAST step stores the
+ * updated columns of the left and/or right block straight into dst* -- normally buffers of the neighbour
+ * GPUs mapped through CUDA IPC, reached by peer stores over NVLink -- instead of local memory (NULL = keep
+ * that block local).  That step rewrites every block pair, rotated or not, so the destination holds the
+ * complete block; the local copy of a redirected block is stale afterwards.  The caller orders the rounds
+ * (a barrier between the end of this call on all ranks and the first use of the received blocks).
+ * svdj_ipc_*: device allocations other processes can map, and their 64-byte handles (cudaIpcMemHandle_t).
+ */
+int svdj_ring_phase_send_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right,
+                                size_t lda, double *dV_left, double *dV_right, size_t ldv, int phase, double tol,
+                                int inner_sweeps, unsigned long long *d_counters, double *dstA_left,
+                                double *dstV_left, double *dstA_right, double *dstV_right, void *stream);
+int svdj_ipc_alloc(size_t bytes, void **dptr);
+int svdj_ipc_free(void *dptr);
+int svdj_ipc_export(void *dptr, unsigned char *handle64);
+int svdj_ipc_open(const unsigned char *handle64, void **peer_ptr);
+int svdj_ipc_close(void *peer_ptr);
+
 /* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
 size_t svdj_num_steps(size_t n);
 

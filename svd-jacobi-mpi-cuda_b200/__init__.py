@@ -84,6 +84,12 @@ EXPORTS = (
     "svdj_ring_ws_destroy",
     "svdj_ring_phase_device",
     "svdj_ring_finalize_device",
+    "svdj_ring_phase_send_device",
+    "svdj_ipc_alloc",
+    "svdj_ipc_free",
+    "svdj_ipc_export",
+    "svdj_ipc_open",
+    "svdj_ipc_close",
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_last_error",
@@ -117,6 +123,18 @@ def _load() -> C.CDLL:
     lib.svdj_ring_phase_device.restype = i
     lib.svdj_ring_finalize_device.argtypes = [vp, sz, sz, vp, sz, vp, i, vp]
     lib.svdj_ring_finalize_device.restype = i
+    lib.svdj_ring_phase_send_device.argtypes = [vp, sz, sz, sz, vp, vp, sz, vp, vp, sz, i, dbl, i, vp, vp, vp, vp, vp, vp]
+    lib.svdj_ring_phase_send_device.restype = i
+    lib.svdj_ipc_alloc.argtypes = [sz, C.POINTER(C.c_void_p)]
+    lib.svdj_ipc_alloc.restype = i
+    lib.svdj_ipc_free.argtypes = [vp]
+    lib.svdj_ipc_free.restype = i
+    lib.svdj_ipc_export.argtypes = [vp, C.c_char_p]
+    lib.svdj_ipc_export.restype = i
+    lib.svdj_ipc_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.svdj_ipc_open.restype = i
+    lib.svdj_ipc_close.argtypes = [vp]
+    lib.svdj_ipc_close.restype = i
     lib.svdj_step_scratch_doubles.argtypes = [sz, sz]
     lib.svdj_step_scratch_doubles.restype = sz
     lib.svdj_num_steps.argtypes = [sz]

@@ -46,6 +46,14 @@ __device__ __forceinline__ double *col_ptr(const BlockArgs &a, bool is_a, unsign
   return base + (size_t)c * (is_a ? a.lda : a.ldv);
 }
 
+// Where an updated column is written.  Normally the place it was read from; in the last step of a ring
+// round the drivers point the stores of a travelling column block at the neighbour GPU's receive buffer
+// (a peer mapping over NVLink), so that the block exchange rides on the update kernel's own stores.
+__device__ __forceinline__ double *col_ptr_store(const BlockArgs &a, bool is_a, unsigned c) {
+  double *base = is_a ? (c < a.split ? a.A_st : a.A2_st) : (c < a.split ? a.V_st : a.V2_st);
+  return base + (size_t)c * (is_a ? a.lda : a.ldv);
+}
+
 // Block pair idx of step k (1-based).  sched 0: the reference's round-robin over all nb blocks
 // (every pair once per nb-1 steps); sched 1: bipartite, block i of the first half with block
 // (i + k - 1) mod (nb/2) of the second half (every cross pair once per nb/2 steps).
@@ -265,7 +273,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     if (sweep_rot == 0) break;
   }
 
-  if (total_rot > 0) {
+  if (total_rot > 0 || a.force_update) {
     // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  thread (r = tid>>3, c4 = (tid&7)*4) computes 4 entries
     const int r = tid >> 3, c0 = (tid & 7) * 4;
     double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
@@ -315,7 +323,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     wdst[rank_of[c0 + 3] * kD + r] = u3;
   }
   if (tid == 0) {
-    wflag[pair] = total_rot > 0 ? 1 : 0;
+    wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;  // force_update: W = I still moves the columns
     if (a.counters) {
       if (total_rot > 0) atomicAdd(&a.counters->applied, (unsigned long long)total_rot);
       atomicMax(&a.counters->offdiag_bits, fresh_max);
@@ -395,8 +403,8 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
       if (row < limit) {
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-          if (sc[nt][0] != kNoCol) col_ptr(a, isa, sc[nt][0])[row] = d[nt][0];
-          if (sc[nt][1] != kNoCol) col_ptr(a, isa, sc[nt][1])[row] = d[nt][1];
+          if (sc[nt][0] != kNoCol) col_ptr_store(a, isa, sc[nt][0])[row] = d[nt][0];
+          if (sc[nt][1] != kNoCol) col_ptr_store(a, isa, sc[nt][1])[row] = d[nt][1];
         }
       }
     }
@@ -545,8 +553,8 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
         for (int nt = 0; nt < 4; ++nt) {
           const unsigned c0 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg, a.n);
           const unsigned c1 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg + 1, a.n);
-          if (c0 != kNoCol) col_ptr(a, isa, c0)[row] = d[nt][0];
-          if (c1 != kNoCol) col_ptr(a, isa, c1)[row] = d[nt][1];
+          if (c0 != kNoCol) col_ptr_store(a, isa, c0)[row] = d[nt][0];
+          if (c1 != kNoCol) col_ptr_store(a, isa, c1)[row] = d[nt][1];
         }
       }
     }
@@ -692,6 +700,17 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
     a.A2 = a.A2 - (size_t)a.split * a.lda;
     if (a.V2 != nullptr) a.V2 = a.V2 - (size_t)a.split * a.ldv;
   }
+  // store targets: the load buffers unless the caller redirected them (already as plain block bases)
+  a.A_st = a_in.A_st ? a_in.A_st : a_in.A;
+  a.V_st = a_in.V_st ? a_in.V_st : a_in.V;
+  if (a_in.A2 == nullptr || a_in.split >= a_in.n) {
+    a.A2_st = a.A_st;
+    a.V2_st = a.V_st;
+  } else {
+    a.A2_st = (a_in.A2_st ? a_in.A2_st : a_in.A2) - (size_t)a.split * a.lda;
+    double *v2 = a_in.V2_st ? a_in.V2_st : a_in.V2;
+    a.V2_st = v2 ? v2 - (size_t)a.split * a.ldv : nullptr;
+  }
   const unsigned splits = gram_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + 3u) & ~3u;  // k-steps are 4 rows
@@ -699,6 +718,9 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
                        ((reinterpret_cast<uintptr_t>(a.A2) & 15) == 0) &&
                        (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0) &&
                                         ((reinterpret_cast<uintptr_t>(a.V2) & 15) == 0)));
+  const bool st_aligned = ((reinterpret_cast<uintptr_t>(a.A_st) | reinterpret_cast<uintptr_t>(a.A2_st) |
+                            reinterpret_cast<uintptr_t>(a.V_st) | reinterpret_cast<uintptr_t>(a.V2_st)) & 7) == 0;
+  (void)st_aligned;
   const bool staged = aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update();
   constexpr size_t kStageSmem = sizeof(double) * kUpdStages * kTileDoubles;
   if (staged) {

@@ -180,6 +180,11 @@ struct BlockArgs {
   // pass 0: the ordering moves columns from one travelling block to the other, and with the tournament's
   // fixed block 0 the largest column of the last rank then never meets the largest column of rank 0.
   int sort_cols;
+  // Optional store targets (null = store where the column was loaded from): block bases for the first and the
+  // second buffer.  A ring driver sets them, for the last step of a round, to peer-mapped buffers of the
+  // neighbour GPUs.  force_update makes that step rewrite every block pair, rotated or not.
+  double *A_st = nullptr, *A2_st = nullptr, *V_st = nullptr, *V2_st = nullptr;
+  int force_update = 0;
   double tol;
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve

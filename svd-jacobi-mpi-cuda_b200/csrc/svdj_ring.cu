@@ -69,9 +69,10 @@ int svdj_ring_ws_destroy(void *ws) {
   return SVDJ_OK;
 }
 
-int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
-                           double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
-                           int inner_sweeps, unsigned long long *d_counters, void *stream) {
+static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
+                      double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
+                      int inner_sweeps, unsigned long long *d_counters, void *stream, double *dstA_left,
+                      double *dstA_right, double *dstV_left, double *dstV_right, bool redirect_last) {
   RingWorkspace *W = static_cast<RingWorkspace *>(ws);
   if (W == nullptr) return -1;
   if (m == 0 || m != W->m) return -2;
@@ -103,8 +104,75 @@ int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *d
   const unsigned steps = (phase == SVDJ_PHASE_CROSS) ? b.nb / 2 : (unsigned)svdj_num_steps(b.nb);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   for (unsigned k = 1; k <= steps; ++k) {
+    if (redirect_last && k == steps) {
+      // last step of the round: the update kernel stores the travelling blocks where their next owner wants
+      // them (peer-mapped memory of a neighbour GPU) and rewrites every pair, rotated or not
+      b.A_st = dstA_left ? dstA_left : dA_left;
+      b.A2_st = dstA_right ? dstA_right : dA_right;
+      b.V_st = dstV_left ? dstV_left : dV_left;
+      b.V2_st = dstV_right ? dstV_right : dV_right;
+      b.force_update = 1;
+    }
     if (int rc = blk_launch_step(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr)) return rc;
   }
+  return SVDJ_OK;
+}
+
+int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
+                           double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
+                           int inner_sweeps, unsigned long long *d_counters, void *stream) {
+  return ring_phase(ws, m, vrows, w, dA_left, dA_right, lda, dV_left, dV_right, ldv, rotate_v, phase, tol,
+                    inner_sweeps, d_counters, stream, nullptr, nullptr, nullptr, nullptr, false);
+}
+
+int svdj_ring_phase_send_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right,
+                                size_t lda, double *dV_left, double *dV_right, size_t ldv, int phase, double tol,
+                                int inner_sweeps, unsigned long long *d_counters, double *dstA_left,
+                                double *dstV_left, double *dstA_right, double *dstV_right, void *stream) {
+  return ring_phase(ws, m, vrows, w, dA_left, dA_right, lda, dV_left, dV_right, ldv, 1, phase, tol, inner_sweeps,
+                    d_counters, stream, dstA_left, dstA_right, dstV_left, dstV_right, true);
+}
+
+// ---- device memory that other processes can map (CUDA IPC) ------------------------------------------------
+int svdj_ipc_alloc(size_t bytes, void **dptr) {
+  if (dptr == nullptr) return -2;
+  *dptr = nullptr;
+  cudaError_t e = cudaMalloc(dptr, bytes ? bytes : 8);
+  if (e != cudaSuccess) {
+    set_error("svdj_ipc_alloc: cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e));
+    cudaGetLastError();
+    return SVDJ_ERR_ALLOC;
+  }
+  SVDJ_CUDA_TRY(cudaMemset(*dptr, 0, bytes ? bytes : 8));
+  return SVDJ_OK;
+}
+
+int svdj_ipc_free(void *dptr) {
+  if (dptr) SVDJ_CUDA_TRY(cudaFree(dptr));
+  return SVDJ_OK;
+}
+
+int svdj_ipc_export(void *dptr, unsigned char *handle64) {
+  if (dptr == nullptr) return -1;
+  if (handle64 == nullptr) return -2;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  SVDJ_CUDA_TRY(cudaIpcGetMemHandle(&h, dptr));
+  std::memcpy(handle64, &h, 64);
+  return SVDJ_OK;
+}
+
+int svdj_ipc_open(const unsigned char *handle64, void **peer_ptr) {
+  if (handle64 == nullptr) return -1;
+  if (peer_ptr == nullptr) return -2;
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle64, 64);
+  SVDJ_CUDA_TRY(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return SVDJ_OK;
+}
+
+int svdj_ipc_close(void *peer_ptr) {
+  if (peer_ptr) SVDJ_CUDA_TRY(cudaIpcCloseMemHandle(peer_ptr));
   return SVDJ_OK;
 }
 

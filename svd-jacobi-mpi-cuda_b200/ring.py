@@ -13,16 +13,24 @@ one message).  A sweep is a round-robin tournament of the 2P blocks (circle meth
 
 so every pair of columns meets exactly once per sweep, as in the reference's ordering, and the only
 collective is one all-reduce of the rotation count per sweep (the reference barriers every step).
-Block moves are ``torch.distributed`` point-to-point operations batched per round (NCCL send/recv over
-NVLink on GPUs, gloo in the CPU tests); the per-rank compute is libsvdj's block-Jacobi phase
-(``svdj_ring_phase_device``).  The compute backend is injected so that the host logic (tournament,
-exchange, convergence) can be tested on CPU with a stand-in backend; the product backend is
-:class:`GpuBackend` and there is no CPU fallback in this module.
+
+Two ways to move the blocks:
+
+* ``exchange="nccl"``: ``torch.distributed`` point-to-point operations batched per round (grouped
+  ncclSend/ncclRecv over NVLink on GPUs; gloo in the CPU tests).
+* ``exchange="fused"``: no send/recv at all.  Every rank maps its neighbours' block buffers through CUDA
+  IPC; the update kernel of the LAST step of a round stores the travelling blocks straight into the
+  buffers their next owner will read (peer stores over NVLink, tile by tile while the kernel is still
+  multiplying), and a one-element all-reduce orders the rounds.
+
+The per-rank compute is libsvdj's block-Jacobi phase (``svdj_ring_phase_device``).  The compute backend is
+injected so that the host logic (tournament, buffer roles, exchange, convergence) can be tested on CPU with
+a stand-in backend; the product backend is :class:`GpuBackend` and there is no CPU fallback in this module.
 """
 from __future__ import annotations
 
 import ctypes as C
-from typing import Callable, List, Optional, Tuple
+from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
@@ -59,6 +67,37 @@ def tournament_rounds(P: int) -> List[Tuple[List[int], List[int]]]:
     return out
 
 
+def initial_roles(P: int) -> List[Dict]:
+    """Every rank owns four block buffers 0..3: which one is its top, its bottom, and which are spare."""
+    return [{"top": 0, "bottom": 1, "spare": [2, 3]} for _ in range(P)]
+
+
+def advance_roles(P: int, roles: List[Dict]):
+    """Buffer roles after one rotation, for every rank, and the transfers that realise it:
+    (src_rank, src_buffer, dst_rank, dst_buffer).  Deterministic, so every rank computes the same table and
+    a sender knows which buffer of its neighbour is free.  Mirrors :func:`rotate`."""
+    if P == 1:
+        return [dict(r, spare=list(r["spare"])) for r in roles], []
+    new, transfers = [], []
+    for r in range(P):
+        spare = list(roles[r]["spare"])
+        if r == 0:
+            nb = spare.pop()
+            transfers.append((1, roles[1]["bottom"], 0, nb))          # new bottom[0] = old bottom[1]
+            nt = roles[0]["top"]                                       # block 0 never moves
+        else:
+            nt = spare.pop()
+            src = (r - 1, roles[r - 1]["top"]) if r >= 2 else (0, roles[0]["bottom"])
+            transfers.append((src[0], src[1], r, nt))                  # new top[r] = old top[r-1] (old bottom[0] for r = 1)
+            if r < P - 1:
+                nb = spare.pop()
+                transfers.append((r + 1, roles[r + 1]["bottom"], r, nb))  # new bottom[r] = old bottom[r+1]
+            else:
+                nb = roles[r]["top"]                                   # the last rank's top turns the corner
+        new.append({"top": nt, "bottom": nb, "spare": [i for i in range(4) if i != nt and i != nb]})
+    return new, transfers
+
+
 # ----------------------------------------------------------------------------------------------------
 # compute backend on the GPU (the product path)
 # ----------------------------------------------------------------------------------------------------
@@ -88,6 +127,10 @@ class GpuBackend:
         except Exception:
             pass
 
+    def _count(self, phase):
+        nb = 2 * self.w // 16
+        self.launches += 3 * (nb // 2 if phase == PHASE_CROSS else int(self.lib.svdj_num_steps(nb)))
+
     def phase(self, top, bottom, phase: int, counters: torch.Tensor) -> None:
         """top/bottom: Block objects; counters: int64[2] on the device."""
         stream = torch.cuda.current_stream().cuda_stream
@@ -96,8 +139,27 @@ class GpuBackend:
                                              self.tol, self.inner, counters.data_ptr(), stream)
         if rc != 0:
             raise self._err(rc, self._last_error())
-        nb = 2 * self.w // 16
-        self.launches += 3 * (nb // 2 if phase == PHASE_CROSS else int(self.lib.svdj_num_steps(nb)))
+        self._count(phase)
+
+    def phase_send(self, top, bottom, phase: int, counters: torch.Tensor, dst_top: Optional[int],
+                   dst_bottom: Optional[int]) -> None:
+        """Like :meth:`phase`, but the last step stores the updated top / bottom block at the given device
+        addresses (base of a peer-mapped block buffer: A-part first, V-part at + w*lda doubles); None = local."""
+        stream = torch.cuda.current_stream().cuda_stream
+        off = self.w * self.lda * 8
+
+        def split(p):
+            return (p, p + off) if p else (None, None)
+
+        ta, tv = split(dst_top)
+        ba, bv = split(dst_bottom)
+        rc = self.lib.svdj_ring_phase_send_device(self.ws, self.m, self.n, self.w, top.A.data_ptr(),
+                                                  bottom.A.data_ptr(), self.lda, top.V.data_ptr(),
+                                                  bottom.V.data_ptr(), self.ldv, phase, self.tol, self.inner,
+                                                  counters.data_ptr(), ta, tv, ba, bv, stream)
+        if rc != 0:
+            raise self._err(rc, self._last_error())
+        self._count(phase)
 
     def finalize(self, blk, scale_u: bool = True) -> torch.Tensor:
         sigma = torch.empty(self.w, dtype=torch.float64, device=blk.A.device)
@@ -110,12 +172,32 @@ class GpuBackend:
         return sigma
 
 
+class _DeviceMemory:
+    """Lets torch wrap a raw device allocation (``torch.as_tensor`` reads ``__cuda_array_interface__``)."""
+
+    def __init__(self, ptr: int, doubles: int):
+        self.__cuda_array_interface__ = {"shape": (doubles,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
 class Block:
     """One column block: A-part (w columns of m rows) and V-part (w columns of n rows) in one allocation,
-    column-major (row j of the 2-D views is column j)."""
+    column-major (row j of the 2-D views is column j).  With ``ipc=True`` the allocation comes from
+    ``svdj_ipc_alloc`` (plain cudaMalloc) so that a neighbour process can map it."""
 
-    def __init__(self, w: int, m: int, n: int, lda: int, ldv: int, device):
-        self.buf = torch.zeros(w * (lda + ldv), dtype=torch.float64, device=device)
+    def __init__(self, w: int, m: int, n: int, lda: int, ldv: int, device, ipc: bool = False):
+        doubles = w * (lda + ldv)
+        self.raw_ptr = None
+        if ipc:
+            from . import lib, last_error, SvdjError
+            p = C.c_void_p()
+            rc = lib.svdj_ipc_alloc(doubles * 8, C.byref(p))
+            if rc != 0:
+                raise SvdjError(rc, last_error())
+            self.raw_ptr = p.value
+            self._keep = _DeviceMemory(self.raw_ptr, doubles)
+            self.buf = torch.as_tensor(self._keep, device=device)
+        else:
+            self.buf = torch.zeros(doubles, dtype=torch.float64, device=device)
         self.A = self.buf[: w * lda].view(w, lda)
         self.V = self.buf[w * lda:].view(w, ldv)
         self.block_id = -1
@@ -126,13 +208,16 @@ class Block:
 # ----------------------------------------------------------------------------------------------------
 class RingSolver:
     def __init__(self, m: int, n: int, device, group=None, tol: Optional[float] = None, max_sweeps: int = 60,
-                 backend=None, inner_sweeps: int = 0):
+                 backend=None, inner_sweeps: int = 0, exchange: str = "nccl"):
         self.group = group
         self.P = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         P = self.P
         if n % (2 * P) != 0 or (n // (2 * P)) % 16 != 0:
             raise ValueError(f"n = {n} must be a multiple of 32 * world_size = {32 * P} (column blocks of 16)")
+        if exchange not in ("nccl", "fused"):
+            raise ValueError("exchange must be 'nccl' or 'fused'")
+        self.exchange = exchange if P > 1 else "nccl"
         self.m, self.n, self.w = m, n, n // (2 * P)
         self.lda = (m + 15) // 16 * 16   # 128-byte columns
         self.ldv = (n + 15) // 16 * 16
@@ -141,17 +226,60 @@ class RingSolver:
         self.max_sweeps = max_sweeps
         self.backend = backend if backend is not None else GpuBackend(m, n, self.w, self.lda, self.ldv, self.tol,
                                                                     inner_sweeps)
-        mk = lambda: Block(self.w, m, n, self.lda, self.ldv, device)  # noqa: E731
-        self.top, self.bottom = mk(), mk()
-        self.spare = [mk(), mk()]
+        fused = self.exchange == "fused"
+        self.blocks = [Block(self.w, m, n, self.lda, self.ldv, device, ipc=fused) for _ in range(4)]
+        self.roles = initial_roles(P)
         t, b = initial_arrangement(P)
         self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
         self.counters = torch.zeros(2, dtype=torch.int64, device=device)
         self.exchanged_bytes = 0
+        self._arrangements = tournament_rounds(P)
+        self._round = 0
+        self.peer: Dict[int, List[int]] = {}
+        if fused:
+            self._map_neighbours()
+
+    # -- the two active blocks -------------------------------------------------------------------------
+    @property
+    def top(self) -> Block:
+        return self.blocks[self.roles[self.rank]["top"]]
+
+    @property
+    def bottom(self) -> Block:
+        return self.blocks[self.roles[self.rank]["bottom"]]
+
+    def _map_neighbours(self) -> None:
+        """Exchange the IPC handles of the four block buffers and map those of the two ring neighbours."""
+        from . import lib, last_error, SvdjError
+        mine = torch.zeros(4, 64, dtype=torch.uint8)
+        for i, blk in enumerate(self.blocks):
+            h = C.create_string_buffer(64)
+            rc = lib.svdj_ipc_export(blk.raw_ptr, h)
+            if rc != 0:
+                raise SvdjError(rc, last_error())
+            mine[i] = torch.frombuffer(bytearray(h.raw), dtype=torch.uint8)
+        mine = mine.to(self.device)
+        everyone = [torch.empty_like(mine) for _ in range(self.P)]
+        dist.all_gather(everyone, mine, group=self.group)
+        for nb in {(self.rank - 1) % self.P, (self.rank + 1) % self.P} - {self.rank}:
+            ptrs = []
+            for i in range(4):
+                raw = bytes(everyone[nb][i].cpu().numpy().tobytes())
+                p = C.c_void_p()
+                rc = lib.svdj_ipc_open(raw, C.byref(p))
+                if rc != 0:
+                    raise SvdjError(rc, last_error())
+                ptrs.append(p.value)
+            self.peer[nb] = ptrs
 
     # -- data in ----------------------------------------------------------------------------------------
     def fill_local(self, column_source: Callable[[int, int], torch.Tensor]) -> None:
-        """column_source(col0, count) -> (count, m) tensor with the columns [col0, col0+count) of A."""
+        """column_source(col0, count) -> (count, m) tensor with the columns [col0, col0+count) of A.
+        Resets the tournament to round 0."""
+        self.roles = initial_roles(self.P)
+        self._round = 0
+        t, b = initial_arrangement(self.P)
+        self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
         for blk in (self.top, self.bottom):
             c0 = blk.block_id * self.w
             blk.A.zero_()
@@ -159,6 +287,8 @@ class RingSolver:
             blk.V.zero_()
             idx = torch.arange(self.w, device=self.device)
             blk.V[idx, c0 + idx] = 1.0  # V = I (main.cu:462-474), this block's columns of it
+        if self.exchange == "fused":
+            self._fence()  # nobody writes into a neighbour before every rank has finished (re)initialising
 
     def scatter_from_root(self, A_root: Optional[torch.Tensor]) -> None:
         """Rank 0 holds A as an (n, m) tensor (column-major m x n); every rank receives its two blocks."""
@@ -166,14 +296,13 @@ class RingSolver:
             self.fill_local(lambda c0, cnt: A_root[c0:c0 + cnt])
             return
         ops, keep = [], []
+        t, b = initial_arrangement(self.P)
         if self.rank == 0:
-            t, b = initial_arrangement(self.P)
             for r in range(1, self.P):
                 for bid in (t[r], b[r]):
                     piece = A_root[bid * self.w:(bid + 1) * self.w].contiguous()
                     keep.append(piece)
                     ops.append(dist.P2POp(dist.isend, piece, r, self.group))
-            local = {0: A_root}
         else:
             recv = [torch.empty(self.w, self.m, dtype=torch.float64, device=self.device) for _ in range(2)]
             for piece in recv:
@@ -183,62 +312,66 @@ class RingSolver:
         if self.rank == 0:
             self.fill_local(lambda c0, cnt: A_root[c0:c0 + cnt])
         else:
-            pieces = {self.top.block_id * self.w: recv[0], self.bottom.block_id * self.w: recv[1]}
+            pieces = {t[self.rank] * self.w: recv[0], b[self.rank] * self.w: recv[1]}
             self.fill_local(lambda c0, cnt: pieces[c0])
 
     # -- one rotation of the blocks ---------------------------------------------------------------------
-    def _exchange(self) -> None:
-        P, r = self.P, self.rank
-        if P == 1:
-            return
-        sends, recvs = [], {}
-        # sends of the blocks held now (mirrors rotate())
-        if r == 0:
-            sends.append((self.bottom, 1))
-        else:
-            if r < P - 1:
-                sends.append((self.top, r + 1))
-            sends.append((self.bottom, r - 1))
-        # receives into spare blocks
-        spare = list(self.spare)
-        if r == 0:
-            recvs["bottom"] = (spare.pop(), 1)
-        else:
-            recvs["top"] = (spare.pop(), r - 1)
-            if r < P - 1:
-                recvs["bottom"] = (spare.pop(), r + 1)
-        ops = [dist.P2POp(dist.isend, blk.buf, peer, self.group) for blk, peer in sends]
-        ops += [dist.P2POp(dist.irecv, blk.buf, peer, self.group) for blk, peer in recvs.values()]
-        for req in dist.batch_isend_irecv(ops):
-            req.wait()
-        self.exchanged_bytes += sum(blk.buf.numel() * 8 for blk, _ in sends)
-        # new arrangement: block ids follow rotate(); buffers are swapped, never copied
-        old_top = self.top
-        if r == 0:
-            new_top, new_bottom = old_top, recvs["bottom"][0]
-        elif r == P - 1:
-            new_top, new_bottom = recvs["top"][0], old_top  # the last rank's top turns the corner
-        else:
-            new_top, new_bottom = recvs["top"][0], recvs["bottom"][0]
-        everything = [self.top, self.bottom] + self.spare
-        self.top, self.bottom = new_top, new_bottom
-        self.spare = [b for b in everything if b is not new_top and b is not new_bottom]
+    def _fence(self) -> None:
+        """Orders the rounds of the fused exchange: a one-element all-reduce on the compute stream."""
+        token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        dist.all_reduce(token, group=self.group)
 
+    def _exchange(self) -> None:
+        """NCCL / gloo exchange: send and receive the travelling blocks, then swap buffer roles."""
+        P, r = self.P, self.rank
+        new_roles, transfers = advance_roles(P, self.roles)
+        if P > 1:
+            ops = []
+            for (sr, sb, dr, db) in transfers:
+                if sr == r:
+                    ops.append(dist.P2POp(dist.isend, self.blocks[sb].buf, dr, self.group))
+                    self.exchanged_bytes += self.blocks[sb].buf.numel() * 8
+            for (sr, sb, dr, db) in transfers:
+                if dr == r:
+                    ops.append(dist.P2POp(dist.irecv, self.blocks[db].buf, sr, self.group))
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        self.roles = new_roles
+
+    def _phase_and_move(self, phase: int) -> None:
+        """One round: the local phase, then the rotation of the blocks (separate or fused into the phase)."""
+        if self.exchange == "nccl":
+            self.backend.phase(self.top, self.bottom, phase, self.counters)
+            self._exchange()
+        else:
+            P, r = self.P, self.rank
+            new_roles, transfers = advance_roles(P, self.roles)
+            dst = {"top": None, "bottom": None}
+            for (sr, sb, dr, db) in transfers:
+                if sr == r:
+                    which = "top" if sb == self.roles[r]["top"] else "bottom"
+                    dst[which] = self.peer[dr][db]
+                    self.exchanged_bytes += self.blocks[sb].buf.numel() * 8
+            self.backend.phase_send(self.top, self.bottom, phase, self.counters, dst["top"], dst["bottom"])
+            self._fence()  # every rank's last step has finished writing before anybody reads a received block
+            self.roles = new_roles
+        self._round += 1
+        t, b = self._arrangements[self._round % len(self._arrangements)]
+        self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
+
+    # kept for the tests of the host logic: one rotation without compute
     def _set_ids(self, round_index: int) -> None:
         t, b = self._arrangements[round_index % len(self._arrangements)]
         self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
 
     # -- the solve ---------------------------------------------------------------------------------------
     def solve(self) -> dict:
-        self._arrangements = tournament_rounds(self.P)
         rounds = len(self._arrangements)
         sweeps, converged, applied_total, last_off = 0, False, 0, 0.0
         for sweep in range(self.max_sweeps):
             self.counters.zero_()
             for rd in range(rounds):
-                self.backend.phase(self.top, self.bottom, PHASE_ALL if rd == 0 else PHASE_CROSS, self.counters)
-                self._exchange()
-                self._set_ids(rd + 1)
+                self._phase_and_move(PHASE_ALL if rd == 0 else PHASE_CROSS)
             # one collective per sweep: rotations (sum) and largest off-diagonal cosine (max of the bit patterns)
             if self.P > 1:
                 dist.all_reduce(self.counters[0:1], op=dist.ReduceOp.SUM, group=self.group)

@@ -152,3 +152,30 @@ def test_ring_solver_with_gloo(tmp_path, world, m, n):
     # same singular values as the single-process oracle
     Uo, so, Vo, ost, rc = H.oracle_svd(A0)
     assert H.sigma_error_normwise(s, so) <= 1e-12
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 8])
+def test_buffer_roles_follow_the_tournament(P):
+    """advance_roles() is what both exchanges (send/recv and peer stores) are driven by: every transfer must
+    land in a spare buffer of the receiver and the blocks must end up where rotate() says, round after round."""
+    ring = _ring()
+    roles = ring.initial_roles(P)
+    top, bot = ring.initial_arrangement(P)
+    held = [{roles[q]["top"]: top[q], roles[q]["bottom"]: bot[q]} for q in range(P)]  # buffer -> block id
+    for rd in range(3 * (2 * P - 1)):
+        new, transfers = ring.advance_roles(P, roles)
+        arrived = [dict() for _ in range(P)]
+        for (sr, sb, dr, db) in transfers:
+            assert abs(sr - dr) == 1, "only ring neighbours talk"
+            assert db in roles[dr]["spare"], "a block may only be written into a spare buffer"
+            assert sb in (roles[sr]["top"], roles[sr]["bottom"])
+            arrived[dr][db] = held[sr][sb]
+        top, bot = ring.rotate(top, bot)
+        for q in range(P):
+            for role in ("top", "bottom"):
+                if new[q][role] not in arrived[q]:
+                    arrived[q][new[q][role]] = held[q][new[q][role]]  # stayed in place (or turned the corner)
+            assert arrived[q][new[q]["top"]] == top[q] and arrived[q][new[q]["bottom"]] == bot[q]
+            assert sorted([new[q]["top"], new[q]["bottom"]] + new[q]["spare"]) == [0, 1, 2, 3]
+        roles = new
+        held = [{new[q]["top"]: top[q], new[q]["bottom"]: bot[q]} for q in range(P)]

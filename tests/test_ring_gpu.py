@@ -87,7 +87,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _nccl_worker(rank, world, port, m, n, out_path):
+def _nccl_worker(rank, world, port, m, n, out_path, exchange):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -96,7 +96,7 @@ def _nccl_worker(rank, world, port, m, n, out_path):
     try:
         ring = _ring()
         dev = torch.device("cuda", rank)
-        solver = ring.RingSolver(m, n, dev)
+        solver = ring.RingSolver(m, n, dev, exchange=exchange)
         A0 = H.uniform_matrix(m, n, seed=77)
         solver.scatter_from_root(torch.from_numpy(np.ascontiguousarray(A0.T)).to(dev) if rank == 0 else None)
         st = solver.solve()
@@ -110,11 +110,14 @@ def _nccl_worker(rank, world, port, m, n, out_path):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
-def test_ring_solver_nccl_two_gpus(tmp_path):
+@pytest.mark.parametrize("exchange", ["nccl", "fused"])
+def test_ring_solver_two_gpus(tmp_path, exchange):
+    """exchange='nccl': grouped send/recv between rounds; 'fused': the update kernel of the last step of a round
+    stores the travelling blocks into the neighbour's IPC-mapped buffers (no send/recv)."""
     import torch.multiprocessing as mp
     m, n = 512, 512
     out = str(tmp_path / "r.npz")
-    mp.spawn(_nccl_worker, args=(2, _free_port(), m, n, out), nprocs=2, join=True)
+    mp.spawn(_nccl_worker, args=(2, _free_port(), m, n, out, exchange), nprocs=2, join=True)
     r = np.load(out)
     assert bool(r["converged"])
     _check(H.uniform_matrix(m, n, seed=77), r["U"], r["s"], r["V"])
