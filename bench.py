@@ -216,7 +216,7 @@ def run_ring(args, svdj, world, rank, local_rank):
     ring = importlib.import_module("svd-jacobi-mpi-cuda_b200.ring")
     n = m = args.n
     dev = torch.device("cuda", local_rank)
-    solver = ring.RingSolver(m, n, dev)
+    solver = ring.RingSolver(m, n, dev, exchange=args.exchange)
     w = solver.w
 
     # every rank generates its own columns (counter-based generator: same matrix as the 1-GPU run)
@@ -289,9 +289,9 @@ def run_ring(args, svdj, world, rank, local_rank):
                        "variant": "block", "tol": "m*2^-53 relative",
                        "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20),
                        "parallelism": f"{2 * world} column blocks of {w} columns on a ring of {world} GPUs "
-                                      "(NCCL send/recv between rounds, 1 all-reduce per sweep)"},
+                                      + ("(blocks stored into the neighbours' buffers by the update kernel over NVLink peer mappings, 1 all-reduce per sweep)" if args.exchange == "fused" else "(NCCL send/recv between rounds, 1 all-reduce per sweep)")},
             "sweeps": st["sweeps"], "rotations_applied": st["applied"],
-            "ring": {"bytes_sent_per_rank_per_solve": sent_per_solve, "rounds_per_sweep": 2 * world - 1},
+            "ring": {"bytes_sent_per_rank_per_solve": sent_per_solve, "rounds_per_sweep": 2 * world - 1, "exchange": args.exchange},
             "roofline": None, "cpu_baseline": None,
             "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
                     "d2h_bytes_per_step": (m * n + n * n + n) * 8},
@@ -466,6 +466,7 @@ def main():
     ap.add_argument("--size", "--n", dest="n", type=int, default=4096)
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"], help="N > 1: how column blocks move")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
