@@ -244,6 +244,22 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     }
   }
 
+  // Columns whose norm falls below tol * (largest column norm of the input) are numerically zero: their
+  // direction is rounding noise and no relative test on them can ever pass.  They are left alone
+  // (rank-deficient inputs, m < n).  One pass over A and n doubles to the host, before the clock starts.
+  if (o.threshold_mode == SVDJ_THRESH_REL) {
+    if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+    if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+    std::vector<double> hn(n);
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(hn.data(), d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+    double mx = 0.0;
+    for (double v : hn) mx = std::max(mx, v);
+    const double fl = o.tol * mx;
+    a.floor2 = b.floor2 = fl * fl;
+    st.launches += 1;
+  }
+
   SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, stream));
   unsigned long long step_launches = 0;
   bool converged = false;
@@ -297,7 +313,9 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   SVDJ_CUDA_TRY(cudaEventRecord(ev1.e, stream));
 
   // ---- finalisation -----------------------------------------------------------------------------
-  if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+  if (d_norms.p == nullptr) {
+    if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+  }
   if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
   st.launches += 1;
   const bool scale_u = (jobu == SVDJ_ALLVEC || jobu == SVDJ_SOMEVEC);

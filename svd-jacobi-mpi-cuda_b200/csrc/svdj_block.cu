@@ -214,8 +214,9 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     for (unsigned i = tid; i < kD * kD; i += 256) {
       const int r = i >> 5, c = i & 31;
       if (r < c) {
-        const double den = sqrt(Gb[0][r][r] * Gb[0][c][c]);
-        const double off = den > 0.0 ? fabs(Gb[0][r][c]) / den : 0.0;
+        const double grr = Gb[0][r][r], gcc = Gb[0][c][c];
+        const double den = sqrt(grr * gcc);
+        const double off = (den > 0.0 && grr > a.floor2 && gcc > a.floor2) ? fabs(Gb[0][r][c]) / den : 0.0;
         mx = fmax(mx, off);
       }
     }
@@ -239,7 +240,8 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
       const double al = Gb[cur][p2][q2], be = Gb[cur][p2][p2], ga = Gb[cur][q2][q2];
       const double g11 = Gb[cur][p1][p2], g12 = Gb[cur][p1][q2], g21 = Gb[cur][q1][p2], g22 = Gb[cur][q1][q2];
       const double wp0 = W[j1][p2], wq0 = W[j1][q2], wp1 = W[j1 + 16][p2], wq1 = W[j1 + 16][q2];
-      const bool rot = al * al > tol2 * be * ga;  // |alpha| > tol sqrt(beta gamma), lib/JacobiMethods.cu:462/466
+      // |alpha| > tol sqrt(beta gamma) (lib/JacobiMethods.cu:462/466), and neither column numerically zero
+      const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
       double c2 = 1.0, s2 = 0.0;
       if (rot) fast_rotation(al, be, ga, c2, s2);
       const unsigned mask = __ballot_sync(0xffffffffu, rot) & 0xffffu;

@@ -77,11 +77,17 @@ struct Rot {
   double c, s;
 };
 
+// floor2: squared norm below which a column counts as numerically zero (0 = no floor).  Without it the
+// null columns of a rank-deficient or m < n input keep "rotating" for ever: their direction is rounding
+// noise, so their cosines never fall under a relative tolerance.
 __host__ __device__ inline bool rotation_from_gram(double alpha, double beta, double gamma, double tol,
-                                                   int threshold_mode, Rot &r, double &offdiag) {
+                                                   int threshold_mode, Rot &r, double &offdiag,
+                                                   double floor2 = 0.0) {
   const double denom = sqrt(beta * gamma);
-  offdiag = denom > 0.0 ? fabs(alpha) / denom : 0.0;
-  const bool rotate = (threshold_mode == SVDJ_THRESH_ABS) ? (fabs(alpha) > tol) : (fabs(alpha) > tol * denom);
+  const bool live = beta > floor2 && gamma > floor2;
+  offdiag = (denom > 0.0 && live) ? fabs(alpha) / denom : 0.0;
+  const bool rotate =
+      live && ((threshold_mode == SVDJ_THRESH_ABS) ? (fabs(alpha) > tol) : (fabs(alpha) > tol * denom));
   if (!rotate) {
     r.c = 1.0;
     r.s = 0.0;
@@ -152,6 +158,7 @@ struct StepArgs {
   double tol;
   int threshold_mode;
   SweepCounters *counters;  // may be null
+  double floor2 = 0.0;      // columns with squared norm <= floor2 are treated as zero (never rotated)
 };
 
 // Level-1 fused step (svdj_l1.cu).  k = 1-based step of the reference ordering.
@@ -189,6 +196,7 @@ struct BlockArgs {
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
   SweepCounters *counters;  // may be null
+  double floor2 = 0.0;      // columns with squared norm <= floor2 are treated as zero (never rotated)
 };
 // Optional timing of the update kernel (the dominant, HBM-bound one) of a step: events recorded around it
 // and a device counter that receives the number of block pairs it really updated.

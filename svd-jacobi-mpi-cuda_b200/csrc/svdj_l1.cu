@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(THREADS) l1_pair_reg_kernel(const StepArgs a, 
       gamma = fma(xq[j].y, xq[j].y, gamma);
     }
     block_sum3<THREADS>(alpha, beta, gamma, red);
-    rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag);
+    rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag, a.floor2);
     if (rotate) {
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(THREADS) l1_pair_reg_kernel(const StepArgs a, 
       gamma = fma(xq[j], xq[j], gamma);
     }
     block_sum3<THREADS>(alpha, beta, gamma, red);
-    rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag);
+    rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag, a.floor2);
     if (rotate) {
 #pragma unroll
       for (int j = 0; j < EPT; ++j) {
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(kSplitThreads) l1_rotate_split_kernel(const St
   }
   Rot r;
   double offdiag;
-  const bool rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag);
+  const bool rotate = rotation_from_gram(alpha, beta, gamma, a.tol, a.threshold_mode, r, offdiag, a.floor2);
   if (threadIdx.x == 0 && blockIdx.y == 0) publish_pair(a.counters, rotate, offdiag);
   if (!rotate) return;
 

@@ -174,3 +174,26 @@ def test_qr_preconditioned_front_end(svdj, qr_steps):
     assert H.sigma_error_normwise(s, np.sort(sigma)[::-1]) <= 1e-12
     q = H.svd_quality(A0, U, s, V)
     assert max(q.values()) <= 10 * n * H.EPS, q
+
+
+@pytest.mark.parametrize("variant", ["level1", "block"])
+@pytest.mark.parametrize("m,n", [(64, 100), (40, 72), (96, 96 + 33)])
+def test_more_columns_than_rows(svdj, variant, m, n):
+    """m < n: n - m columns are numerically zero at convergence; they must not keep the sweeps alive.
+    (The reference assumes a square matrix; this is the contract of include/svdj.h for the general case:
+    min(m,n) singular values, U in the first min(m,n) columns of A, V n x n orthogonal.)"""
+    A0 = H.normal_matrix(m, n, seed=m + n)
+    v = svdj.VARIANT_LEVEL1 if variant == "level1" else svdj.VARIANT_BLOCK
+    A = A0.copy(order="F")
+    s = np.zeros(m)
+    V = np.zeros((n, n), order="F")
+    st = svdj.dgesvd(svdj.AllVec, svdj.AllVec, m, n, A, m, s, V, n, svdj.default_opts(variant=v))
+    assert st.converged == 1 and st.sweeps <= 20
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    U = A[:, :m]
+    bound = 10 * n * H.EPS
+    assert np.abs(U.T @ U - np.eye(m)).max() <= bound
+    assert np.abs(V.T @ V - np.eye(n)).max() <= bound
+    assert np.linalg.norm(A0 - (U * s) @ V[:, :m].T) <= bound * np.linalg.norm(A0)
+    # the trailing columns of A are the (numerically zero) images of the null space
+    assert np.abs(A[:, m:]).max() <= 1e-12 * s[0]
