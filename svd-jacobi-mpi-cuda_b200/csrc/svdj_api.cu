@@ -169,8 +169,13 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   SVDJ_CUDA_TRY(cudaMemsetAsync(d_counters.p, 0, sizeof(SweepCounters) * (size_t)o.max_sweeps, stream));
   DevBuf d_gpart, d_w, d_wflag;
   if (block) {
-    size_t gp = 0, wd = 0, fl = 0;
+    // sized for either block width (the 32-wide kernels need more of everything per pair, for half the pairs)
+    size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
     blk_scratch_sizes(m, n, &gp, &wd, &fl);
+    blk32_scratch_sizes(m, n, &gp2, &wd2, &fl2);
+    gp = std::max(gp, gp2);
+    wd = std::max(wd, wd2);
+    fl = std::max(fl, fl2);
     if (int rc = d_gpart.alloc(sizeof(double) * gp)) return rc;
     if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
     if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
@@ -183,10 +188,28 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     st.launches += 1;
   }
 
-  const unsigned nb = blk_num_blocks(n);
+  // block width: 16 by default; 32 on request (opts.block == 32 or SVDJ_BLOCK=32) when the layout allows it
+  bool wide = false;
+  if (block) {
+    int want = o.block;
+    if (const char *env = std::getenv("SVDJ_BLOCK")) want = std::atoi(env);
+    if (want == 32 && blk32_num_blocks(n) >= 2) {
+      BlockArgs probe_args;
+      probe_args.A = dA;
+      probe_args.lda = lda;
+      probe_args.V = dV;
+      probe_args.ldv = ldv;
+      probe_args.rotate_v = rotate_v ? 1 : 0;
+      probe_args.nb = blk32_num_blocks(n);
+      probe_args.A2 = nullptr;
+      wide = blk32_supported(probe_args);
+    }
+  }
+  const unsigned nb = wide ? blk32_num_blocks(n) : blk_num_blocks(n);
   const unsigned steps = (unsigned)svdj_num_steps(block ? nb : n);
-  // column pairs looked at per step: n/2 on the level-1 path, 496 per block pair on the block path
-  const unsigned long long pairs_per_step = block ? (unsigned long long)(nb / 2) * 496ull : n / 2;
+  // column pairs looked at per step: n/2 on the level-1 path, 496 (b = 16) or 2016 (b = 32) per block pair
+  const unsigned long long pairs_per_step =
+      block ? (unsigned long long)(nb / 2) * (wide ? 2016ull : 496ull) : n / 2;
 
   BlockArgs b;
   b.A = dA;
@@ -275,8 +298,8 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
           probes[probes_used].active_pairs = d_probe.as<unsigned long long>();
           probe = &probes[probes_used++];
         }
-        if (int rc = blk_launch_step(b, k, d_gpart.as<double>(), d_w.as<double>(), d_wflag.as<int>(), stream,
-                                     &step_launches, probe))
+        if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, d_gpart.as<double>(), d_w.as<double>(),
+                                                                  d_wflag.as<int>(), stream, &step_launches, probe))
           return rc;
       } else {
         if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
@@ -375,6 +398,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     st.step_kernel_ms = probe_launches ? probe_ms / (double)probe_launches : 0.0;
     st.step_kernel_launches = probe_launches;
     st.probe_block_pairs = active;
+    st.reserved = wide ? 32 : 16;  // block width that ran
   }
   if (o.threshold_mode == SVDJ_THRESH_REL && !converged) return SVDJ_NOT_CONVERGED;
   return SVDJ_OK;

@@ -1,0 +1,515 @@
+// svdj_block32.cu -- the block-Jacobi step with column blocks of 32 (block pairs of 64 columns).
+//
+// Same three kernels as svdj_block.cu (Gram, eigen-solve, update), twice as wide.  Per sweep the flops are
+// the same (10 n^3 at m = n) but there are half as many steps, so half the HBM traffic (a step always touches
+// all of A and V once), half the launches and half the eigen-solve latencies; the update kernel moves from the
+// HBM roofline to the FP64 tensor roofline (0.31 b flop/B = 10 at b = 32, ridge 5.7).  Aligned layouts only
+// (even leading dimensions, 16-byte aligned bases): the callers fall back to the b = 16 kernels otherwise.
+#include <cstdlib>
+
+#include "svdj_block_dev.cuh"
+
+namespace svdj {
+
+static constexpr int kB32 = 32;
+static constexpr int kD64 = 64;                 // columns of a block pair
+static constexpr int kTG = 8;                   // 8 x 8 tiles per side
+static constexpr int kGramTiles32 = 36;         // upper triangle of the 8 x 8 grid of tiles
+static constexpr int kGramPart32 = kGramTiles32 * 64;
+static constexpr int kMaxPairs32 = 2048;
+
+__device__ __forceinline__ unsigned slot_col32(unsigned I, unsigned J, unsigned s, unsigned n) {
+  const unsigned c = (s < kB32) ? I * kB32 + s : J * kB32 + (s - kB32);
+  return c < n ? c : kNoCol;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: partial Gram matrices of the 64-column panels.  grid (block pairs, row splits), 4 warps.  Tiles of
+// 64 rows x 64 columns come in through a 3-stage cp.async pipeline.  The 36 output tiles do not fit one
+// warp's registers, so warps (0,2) accumulate the even-numbered tiles and warps (1,3) the odd ones, each
+// over half of the tile's rows.
+// ------------------------------------------------------------------------------------------------
+static constexpr int kG32Rows = 64;
+static constexpr int kG32Stride = kG32Rows + 4;
+static constexpr int kG32TileDoubles = kD64 * kG32Stride;
+static constexpr int kG32Stages = 3;
+
+template <int GSEL>
+__device__ __forceinline__ void gram32_ksteps(const double *__restrict__ tile, double (&acc)[18][2]) {
+  // tile points at (row 32 rh + tg, column g) of the stage; 8 k-steps of 4 rows
+#pragma unroll 2
+  for (int ks = 0; ks < 8; ++ks) {
+    double f[kTG];
+#pragma unroll
+    for (int gi = 0; gi < kTG; ++gi) f[gi] = tile[(8 * gi) * kG32Stride + 4 * ks];
+    int t = 0;
+#pragma unroll
+    for (int ti = 0; ti < kTG; ++ti)
+#pragma unroll
+      for (int tj = ti; tj < kTG; ++tj) {
+        if ((t & 1) == GSEL) dmma884(acc[t >> 1][0], acc[t >> 1][1], f[ti], f[tj]);
+        ++t;
+      }
+  }
+}
+
+__global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, const unsigned k,
+                                                         const unsigned rows_per_split,
+                                                         double *__restrict__ gpart) {
+  extern __shared__ __align__(16) double tiles[];  // kG32Stages x 64 columns x kG32Stride; reused for the reduction
+  const Pair bp = block_pair(a, k, blockIdx.x);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+  const unsigned r0 = blockIdx.y * rows_per_split;  // a multiple of 64
+  const unsigned r1 = min(a.m, r0 + rows_per_split);
+  const unsigned ntiles = r0 < r1 ? (r1 - r0 + kG32Rows - 1) / kG32Rows : 0;
+
+  auto issue_tile = [&](unsigned t, int stage) {
+    const unsigned row = r0 + t * kG32Rows + 2 * lane;
+    double *dst = tiles + stage * kG32TileDoubles + 2 * lane;
+#pragma unroll 4
+    for (int i = 0; i < 16; ++i) {
+      const unsigned slot = warp + 4 * i;
+      const unsigned c = slot_col32(bp.p, bp.q, slot, a.n);
+      int bytes = 0;
+      const double *src = a.A;
+      if (c != kNoCol && row < r1) {
+        bytes = (row + 1 < r1) ? 16 : 8;
+        src = col_ptr(a, true, c) + row;
+      }
+      cp_async16(dst + slot * kG32Stride, src, bytes);
+    }
+  };
+
+  unsigned issued = 0;
+#pragma unroll
+  for (int s = 0; s < kG32Stages - 1; ++s) {
+    if (issued < ntiles) {
+      issue_tile(issued, s);
+      ++issued;
+    }
+    cp_async_commit();
+  }
+  double acc[18][2];
+#pragma unroll
+  for (int t = 0; t < 18; ++t) acc[t][0] = acc[t][1] = 0.0;
+  const unsigned gsel = warp & 1, rh = warp >> 1;
+
+  for (unsigned t = 0; t < ntiles; ++t) {
+    cp_async_wait<kG32Stages - 2>();
+    __syncthreads();
+    if (issued < ntiles) {
+      issue_tile(issued, (int)(issued % kG32Stages));
+      ++issued;
+    }
+    cp_async_commit();
+    const double *tile = tiles + (t % kG32Stages) * kG32TileDoubles + g * kG32Stride + 32 * rh + tg;
+    if (gsel == 0) gram32_ksteps<0>(tile, acc);
+    else gram32_ksteps<1>(tile, acc);
+  }
+  cp_async_wait<0>();
+  __syncthreads();  // the tile buffers become the reduction buffer: [4 warps][18 tiles][64]
+  double *red = tiles;
+#pragma unroll
+  for (int t = 0; t < 18; ++t) {
+    red[(warp * 18 + t) * 64 + lane * 2 + 0] = acc[t][0];
+    red[(warp * 18 + t) * 64 + lane * 2 + 1] = acc[t][1];
+  }
+  __syncthreads();
+  double *dst = gpart + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * kGramPart32;
+  for (unsigned i = threadIdx.x; i < kGramPart32; i += 128) {
+    const unsigned t = i >> 6, e = i & 63;
+    const unsigned gs = t & 1, lt = t >> 1;  // tile t lives in warps gs and gs + 2 as local tile lt
+    dst[i] = red[((gs)*18 + lt) * 64 + e] + red[((gs + 2) * 18 + lt) * 64 + e];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: eigen-decomposition of the 64 x 64 Gram matrix, cyclic two-sided Jacobi in shared memory, 1024 threads:
+// warp j1, lane j2 owns the 2 x 2 block G[{p1,q1}][{p2,q2}]; each warp computes the 32 rotations of a step in
+// its 32 lanes (lane = pair index) and fetches its own row rotation by shuffle; one barrier per step.
+// ------------------------------------------------------------------------------------------------
+static constexpr int kE32Stride = kD64 + 1;
+static constexpr size_t kE32Smem = sizeof(double) * 4 * kD64 * kE32Stride;
+
+__device__ __forceinline__ void circle_pair64(int t, int j, int &p, int &q) {
+  int x, y;
+  if (j == 0) {
+    x = t;
+    y = kD64 - 1;
+  } else {
+    x = t + j;
+    x = x >= kD64 - 1 ? x - (kD64 - 1) : x;
+    y = t - j;
+    y = y < 0 ? y + (kD64 - 1) : y;
+  }
+  p = min(x, y);
+  q = max(x, y);
+}
+
+__global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
+                                                         const double *__restrict__ gpart, double *__restrict__ wbuf,
+                                                         int *__restrict__ wflag) {
+  extern __shared__ __align__(16) double sm[];
+  double(*G0)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm);
+  double(*G1)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + kD64 * kE32Stride);
+  double(*W)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + 2 * kD64 * kE32Stride);
+  double(*T)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + 3 * kD64 * kE32Stride);
+  __shared__ unsigned long long fresh_max;
+  __shared__ int rank_of[kD64];
+  __shared__ int valid[kD64];
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  const unsigned pair = blockIdx.x;
+
+  const double *src = gpart + (size_t)pair * splits * kGramPart32;
+  for (unsigned i = tid; i < kGramPart32; i += 1024) {
+    double s = 0.0;
+    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+    const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
+    int ti = 0, rem = t;  // t -> (ti, tj): rows of 8, 7, ..., 1 tiles
+    while (rem >= kTG - ti) {
+      rem -= kTG - ti;
+      ++ti;
+    }
+    const int tj = ti + rem;
+    const int r = 8 * ti + (l >> 2), c = 8 * tj + 2 * (l & 3) + e;
+    G0[r][c] = s;
+    if (ti != tj) G0[c][r] = s;
+  }
+  for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
+  if (tid == 0) fresh_max = 0ull;
+  __syncthreads();
+
+  {
+    double mx = 0.0;
+    for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
+      const int r = i >> 6, c = i & 63;
+      if (r < c) {
+        const double grr = G0[r][r], gcc = G0[c][c];
+        const double den = sqrt(grr * gcc);
+        const double off = (den > 0.0 && grr > a.floor2 && gcc > a.floor2) ? fabs(G0[r][c]) / den : 0.0;
+        mx = fmax(mx, off);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(mx));
+  }
+
+  int total_rot = 0;
+  int cur = 0;
+  const int j1 = tid >> 5, j2 = lane;
+  const double tol2 = a.tol * a.tol;
+  for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+    int sweep_rot = 0;
+    for (int t = 0; t < kD64 - 1; ++t) {
+      double(*Gc)[kE32Stride] = cur ? G1 : G0;
+      double(*Gn)[kE32Stride] = cur ? G0 : G1;
+      int p2, q2, p1, q1;
+      circle_pair64(t, j2, p2, q2);
+      circle_pair64(t, j1, p1, q1);
+      const double al = Gc[p2][q2], be = Gc[p2][p2], ga = Gc[q2][q2];
+      const double g11 = Gc[p1][p2], g12 = Gc[p1][q2], g21 = Gc[q1][p2], g22 = Gc[q1][q2];
+      const double wp0 = W[j1][p2], wq0 = W[j1][q2], wp1 = W[j1 + 32][p2], wq1 = W[j1 + 32][q2];
+      const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
+      double c2 = 1.0, s2 = 0.0;
+      if (rot) fast_rotation(al, be, ga, c2, s2);
+      const unsigned mask = __ballot_sync(0xffffffffu, rot);
+      if (mask == 0u) continue;  // every warp sees the same 32 decisions
+      sweep_rot += __popc(mask);
+      const double c1 = __shfl_sync(0xffffffffu, c2, j1), s1 = __shfl_sync(0xffffffffu, s2, j1);
+      const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
+      const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
+      double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
+      double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
+      if (j1 == j2 && s1 != 0.0) {
+        n12 = 0.0;
+        n21 = 0.0;
+      }
+      Gn[p1][p2] = n11;
+      Gn[p1][q2] = n12;
+      Gn[q1][p2] = n21;
+      Gn[q1][q2] = n22;
+      W[j1][p2] = c2 * wp0 - s2 * wq0;
+      W[j1][q2] = s2 * wp0 + c2 * wq0;
+      W[j1 + 32][p2] = c2 * wp1 - s2 * wq1;
+      W[j1 + 32][q2] = s2 * wp1 + c2 * wq1;
+      cur ^= 1;
+      __syncthreads();
+    }
+    total_rot += sweep_rot;
+    if (sweep_rot == 0) break;
+  }
+
+  if (total_rot > 0 || a.force_update) {
+    double(*Gc)[kE32Stride] = cur ? G1 : G0;
+    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W); thread (r = tid >> 4, c0 = (tid & 15) * 4) computes 4 entries
+    const int r = tid >> 4, c0 = (tid & 15) * 4;
+    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+#pragma unroll 8
+    for (int k2 = 0; k2 < kD64; ++k2) {
+      const double wr = W[k2][r];
+      t0 = fma(wr, W[k2][c0 + 0], t0);
+      t1 = fma(wr, W[k2][c0 + 1], t1);
+      t2 = fma(wr, W[k2][c0 + 2], t2);
+      t3 = fma(wr, W[k2][c0 + 3], t3);
+    }
+    T[r][c0 + 0] = (r == c0 + 0 ? 1.5 : 0.0) - 0.5 * t0;
+    T[r][c0 + 1] = (r == c0 + 1 ? 1.5 : 0.0) - 0.5 * t1;
+    T[r][c0 + 2] = (r == c0 + 2 ? 1.5 : 0.0) - 0.5 * t2;
+    T[r][c0 + 3] = (r == c0 + 3 ? 1.5 : 0.0) - 0.5 * t3;
+    if (tid < kD64) {
+      const Pair bp = block_pair(a, k, pair);
+      valid[tid] = slot_col32(bp.p, bp.q, tid, a.n) != kNoCol;
+    }
+    __syncthreads();
+    if (tid < kD64) {  // output slot of column tid: eigenvalues descending over the valid slots (single GPU only)
+      int out = tid;
+      if (a.sort_cols && valid[tid]) {
+        const double di = Gc[tid][tid];
+        int rk = 0;
+        for (int j = 0; j < kD64; ++j) {
+          const double dj = Gc[j][j];
+          rk += (valid[j] && (dj > di || (dj == di && j < (int)tid))) ? 1 : 0;
+        }
+        int seen = 0;
+        for (int j = 0; j < kD64; ++j) {
+          if (valid[j]) {
+            if (seen == rk) {
+              out = j;
+              break;
+            }
+            ++seen;
+          }
+        }
+      }
+      rank_of[tid] = out;
+    }
+    __syncthreads();
+    double u0 = 0, u1 = 0, u2 = 0, u3 = 0;
+#pragma unroll 8
+    for (int k2 = 0; k2 < kD64; ++k2) {
+      const double wr = W[r][k2];
+      u0 = fma(wr, T[k2][c0 + 0], u0);
+      u1 = fma(wr, T[k2][c0 + 1], u1);
+      u2 = fma(wr, T[k2][c0 + 2], u2);
+      u3 = fma(wr, T[k2][c0 + 3], u3);
+    }
+    double *wdst = wbuf + (size_t)pair * kD64 * kD64;  // column-major: wdst[c * 64 + r]
+    wdst[rank_of[c0 + 0] * kD64 + r] = u0;
+    wdst[rank_of[c0 + 1] * kD64 + r] = u1;
+    wdst[rank_of[c0 + 2] * kD64 + r] = u2;
+    wdst[rank_of[c0 + 3] * kD64 + r] = u3;
+  }
+  if (tid == 0) {
+    wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;
+    if (a.counters) {
+      if (total_rot > 0) atomicAdd(&a.counters->applied, (unsigned long long)total_rot);
+      atomicMax(&a.counters->offdiag_bits, fresh_max);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: X <- X W, Y <- Y W for the 64-column panels.  One persistent CTA of 8 warps per SM walks the flat list
+// of 128-row x 64-column tiles of the block pairs that rotated; tiles arrive through a 2-stage cp.async
+// pipeline (1 KiB contiguous per pair of warps); W (64 x 64) sits in shared memory and feeds the DMMA
+// B-fragments, each fragment serving the two 8-row halves of the warp's 16 rows.
+// ------------------------------------------------------------------------------------------------
+static constexpr int kU32Rows = 128;
+static constexpr int kU32Stride = kU32Rows + 4;
+static constexpr int kU32TileDoubles = kD64 * kU32Stride;
+static constexpr int kU32WStride = kD64 + 4;
+static constexpr size_t kU32Smem = sizeof(double) * (2 * kU32TileDoubles + kD64 * kU32WStride);
+
+__global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a, const unsigned k,
+                                                             const double *__restrict__ wbuf,
+                                                             const int *__restrict__ wflag, const unsigned pairs,
+                                                             unsigned long long *__restrict__ active_out) {
+  extern __shared__ __align__(16) double sm[];
+  double *tiles = sm;                          // 2 stages
+  double *Wsm = sm + 2 * kU32TileDoubles;      // Wsm[c * kU32WStride + k] = W[k][c]
+  __shared__ unsigned short active[kMaxPairs32];
+  __shared__ unsigned n_active_s;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned g = lane >> 2, tg = lane & 3;
+
+  if (warp == 0) {
+    unsigned cnt = 0;
+    for (unsigned base = 0; base < pairs; base += 32) {
+      const unsigned p = base + lane;
+      const bool f = p < pairs && wflag[p] != 0;
+      const unsigned mask = __ballot_sync(0xffffffffu, f);
+      if (f) active[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)p;
+      cnt += __popc(mask);
+    }
+    if (lane == 0) {
+      n_active_s = cnt;
+      if (active_out != nullptr && blockIdx.x == 0) *active_out += cnt;
+    }
+  }
+  __syncthreads();
+  const unsigned n_active = n_active_s;
+  const unsigned tpa = (a.m + kU32Rows - 1) / kU32Rows;
+  const unsigned tpv = a.rotate_v ? (a.vrows + kU32Rows - 1) / kU32Rows : 0;
+  const unsigned tpp = tpa + tpv;
+  const unsigned long long total = (unsigned long long)n_active * tpp;
+  const unsigned t0 = (unsigned)(total * blockIdx.x / gridDim.x);
+  const unsigned t1 = (unsigned)(total * (blockIdx.x + 1) / gridDim.x);
+  if (t0 >= t1) return;
+
+  auto issue_tile = [&](unsigned tau, int stage) {
+    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+    const Pair bp = block_pair(a, k, active[ap]);
+    const bool isa = t < tpa;
+    const unsigned limit = isa ? a.m : a.vrows;
+    const unsigned row = (isa ? t : t - tpa) * kU32Rows + 2 * (32 * (warp & 1) + lane);
+    double *dst = tiles + stage * kU32TileDoubles + 2 * (32 * (warp & 1) + lane);
+#pragma unroll 4
+    for (int i = 0; i < 16; ++i) {
+      const unsigned slot = (warp >> 1) + 4 * i;
+      const unsigned col = slot_col32(bp.p, bp.q, slot, a.n);
+      int bytes = 0;
+      const double *src = a.A;
+      if (col != kNoCol && row < limit) {
+        bytes = (row + 1 < limit) ? 16 : 8;
+        src = col_ptr(a, isa, col) + row;
+      }
+      cp_async16(dst + slot * kU32Stride, src, bytes);
+    }
+  };
+
+  unsigned issued = t0;
+  issue_tile(issued, 0);
+  ++issued;
+  cp_async_commit();
+
+  Pair cur_bp = {0u, 0u};
+  unsigned cur_pair = 0xffffffffu;
+  for (unsigned tau = t0; tau < t1; ++tau) {
+    cp_async_wait<0>();
+    __syncthreads();  // tile tau has landed; everyone is done with the other stage and with the previous W
+    if (issued < t1) {
+      issue_tile(issued, (int)((issued - t0) & 1));
+      ++issued;
+    }
+    cp_async_commit();
+
+    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+    const unsigned pr = active[ap];
+    if (pr != cur_pair) {  // CTA-uniform: a new block pair, load its W
+      cur_pair = pr;
+      cur_bp = block_pair(a, k, pr);
+      const double *w = wbuf + (size_t)pr * kD64 * kD64;
+      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += 256) Wsm[(i >> 6) * kU32WStride + (i & 63)] = w[i];
+      __syncthreads();
+    }
+    const bool isa = t < tpa;
+    const unsigned limit = isa ? a.m : a.vrows;
+    const unsigned row0 = (isa ? t : t - tpa) * kU32Rows + 16 * warp;
+    const double *tile = tiles + ((tau - t0) & 1) * kU32TileDoubles + 16 * warp + g;
+    double af[2][16];
+#pragma unroll
+    for (int ks = 0; ks < 16; ++ks) {
+      af[0][ks] = tile[(4 * ks + tg) * kU32Stride];
+      af[1][ks] = tile[(4 * ks + tg) * kU32Stride + 8];
+    }
+    double d[2][8][2];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
+    const double *wl = Wsm + g * kU32WStride + tg;
+#pragma unroll
+    for (int ks = 0; ks < 16; ++ks) {
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const double bf = wl[(8 * nt) * kU32WStride + 4 * ks];
+        dmma884(d[0][nt][0], d[0][nt][1], af[0][ks], bf);
+        dmma884(d[1][nt][0], d[1][nt][1], af[1][ks], bf);
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const unsigned row = row0 + 8 * h + g;
+      if (row < limit) {
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const unsigned c0 = slot_col32(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg, a.n);
+          const unsigned c1 = slot_col32(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg + 1, a.n);
+          if (c0 != kNoCol) col_ptr_store(a, isa, c0)[row] = d[h][nt][0];
+          if (c1 != kNoCol) col_ptr_store(a, isa, c1)[row] = d[h][nt][1];
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+unsigned blk32_num_blocks(size_t n) { return (unsigned)((n + kB32 - 1) / kB32); }
+
+static unsigned gram32_splits(size_t m, unsigned pairs) {
+  size_t want = (2 * 2 * 148 + pairs - 1) / (pairs ? pairs : 1);  // 2 CTAs per SM, two waves
+  size_t cap = (m + kG32Rows - 1) / kG32Rows;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  if (want > 1024) want = 1024;
+  return (unsigned)want;
+}
+
+void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
+  const unsigned nb = blk32_num_blocks(n);
+  const unsigned pairs = nb / 2;
+  *gpart_doubles = (size_t)pairs * gram32_splits(m, pairs) * kGramPart32;
+  *w_doubles = (size_t)pairs * kD64 * kD64;
+  *flag_ints = pairs;
+}
+
+bool blk32_supported(const BlockArgs &a) {
+  const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
+                       (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0)));
+  return aligned && (a.nb / 2) <= (unsigned)kMaxPairs32 && a.nb >= 2 && a.A2 == nullptr;
+}
+
+int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
+                      unsigned long long *launches, const BlockProbe *probe) {
+  const unsigned pairs = a_in.nb / 2;
+  if (pairs == 0) return SVDJ_OK;
+  BlockArgs a = a_in;  // single buffer only
+  a.split = a.n;
+  a.A2 = a.A;
+  a.V2 = a.V;
+  a.A_st = a.A;
+  a.V_st = a.V;
+  a.A2_st = a.A;
+  a.V2_st = a.V;
+  static const cudaError_t attrs = [] {
+    cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(blk32_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kE32Smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(blk32_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kU32Smem);
+    return e;
+  }();
+  SVDJ_CUDA_TRY(attrs);
+  static const int sm_count = [] {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+  }();
+  const unsigned splits = gram32_splits(a.m, pairs);
+  unsigned rps = (a.m + splits - 1) / splits;
+  rps = (rps + kG32Rows - 1) / kG32Rows * kG32Rows;
+  blk32_gram_kernel<<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
+  blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
+  if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
+  blk32_update_kernel<<<sm_count, 256, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
+  if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  if (launches) *launches += 3;
+  SVDJ_CUDA_TRY(cudaGetLastError());
+  return SVDJ_OK;
+}
+
+}  // namespace svdj

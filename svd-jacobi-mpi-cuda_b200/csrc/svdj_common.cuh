@@ -210,6 +210,13 @@ void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doub
 int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
                     unsigned long long *launches, const BlockProbe *probe = nullptr);
 
+// The same step with column blocks of 32 (svdj_block32.cu); single buffer, aligned layouts only.
+unsigned blk32_num_blocks(size_t n);
+void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
+bool blk32_supported(const BlockArgs &a);
+int blk32_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
+                      unsigned long long *launches, const BlockProbe *probe = nullptr);
+
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st);
 int launch_column_norms(const double *A, size_t lda, size_t m, size_t n, double *norms, cudaStream_t st);

@@ -197,3 +197,19 @@ def test_more_columns_than_rows(svdj, variant, m, n):
     assert np.linalg.norm(A0 - (U * s) @ V[:, :m].T) <= bound * np.linalg.norm(A0)
     # the trailing columns of A are the (numerically zero) images of the null space
     assert np.abs(A[:, m:]).max() <= 1e-12 * s[0]
+
+
+@pytest.mark.parametrize("m,n", [(128, 128), (200, 120), (300, 72), (512, 512), (1030, 260)])
+def test_block_width_32_option(svdj, m, n):
+    """opts.block = 32: the same step with 64-column block pairs (svdj_block32.cu)."""
+    A0 = H.uniform_matrix(m, n, seed=3 * m + n)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK, block=32)
+    assert st.converged == 1 and st.reserved == 32
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    assert np.all(np.diff(s) <= 0)
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * max(m, n) * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+    # same answer as the default width
+    A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st2.reserved == 16 and H.sigma_error_normwise(s, s2) <= 1e-12
