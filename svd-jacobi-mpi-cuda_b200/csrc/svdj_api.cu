@@ -191,8 +191,11 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   // block width: 16 by default; 32 on request (opts.block == 32 or SVDJ_BLOCK=32) when the layout allows it
   bool wide = false;
   if (block) {
+    // 0 = choose: measured on B200 (profiles/r1_block_widths.md) the 64-column block pairs win from n = 4096 up
+    // (half the steps and half the HBM traffic per sweep, fewer sweeps), the 32-column ones below
     int want = o.block;
     if (const char *env = std::getenv("SVDJ_BLOCK")) want = std::atoi(env);
+    if (want == 0) want = (n >= 4096) ? 32 : 16;
     if (want == 32 && blk32_num_blocks(n) >= 2) {
       BlockArgs probe_args;
       probe_args.A = dA;
@@ -228,9 +231,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   b.sort_cols = 1;
   b.tol = o.tol;
   b.threshold_mode = o.threshold_mode;
-  // Two cyclic sweeps of the 32 x 32 eigen-solve per visit: measured to need as few outer sweeps as a fully
-  // converged inner solve, at a third of its latency.  SVDJ_INNER_SWEEPS overrides.
-  b.max_inner_sweeps = 2;
+  // One cyclic sweep of the small eigen-solve per visit below n = 8192, two from there on: a converged inner
+  // solve buys no outer sweeps, and below 8192 the eigen-solve's latency chain costs more
+  // than the one or two outer sweeps the second inner sweep saves.  SVDJ_INNER_SWEEPS overrides.
+  b.max_inner_sweeps = (n >= 8192) ? 2 : 1;
   if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) {
     const int v = std::atoi(env);
     if (v > 0) b.max_inner_sweeps = v;

@@ -124,9 +124,12 @@ __device__ __forceinline__ void circle_pair(int t, int j, int &p, int &q) {
 __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
                                                       const double *__restrict__ gpart, double *__restrict__ wbuf,
                                                       int *__restrict__ wflag) {
-  __shared__ double Gb[2][kD][kD + 1];
-  __shared__ double W[kD][kD + 1];
-  __shared__ double T[kD][kD + 1];
+  // Row stride kD + 2: the rotation inputs G[p][q] of a step satisfy p + q = const (circle method), so their
+  // addresses are (stride - 1) p + const; an odd (stride - 1) spreads them over the banks (stride kD + 1 put
+  // all sixteen pairs on one bank), and the diagonal, (stride + 1) p, stays conflict-free as well.
+  __shared__ double Gb[2][kD][kD + 2];
+  __shared__ double W[kD][kD + 2];
+  __shared__ double T[kD][kD + 2];
   __shared__ unsigned long long fresh_max;
   __shared__ int rank_of[kD];
   const unsigned tid = threadIdx.x, lane = tid & 31;

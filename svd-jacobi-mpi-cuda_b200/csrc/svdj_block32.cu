@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
 // warp j1, lane j2 owns the 2 x 2 block G[{p1,q1}][{p2,q2}]; each warp computes the 32 rotations of a step in
 // its 32 lanes (lane = pair index) and fetches its own row rotation by shuffle; one barrier per step.
 // ------------------------------------------------------------------------------------------------
-static constexpr int kE32Stride = kD64 + 1;
+static constexpr int kE32Stride = kD64 + 2;  // odd (stride - 1): conflict-free rotation inputs, see svdj_block.cu
 static constexpr size_t kE32Smem = sizeof(double) * 4 * kD64 * kE32Stride;
 
 __device__ __forceinline__ void circle_pair64(int t, int j, int &p, int &q) {
@@ -311,21 +311,25 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3: X <- X W, Y <- Y W for the 64-column panels.  One persistent CTA of 8 warps per SM walks the flat list
+// K3: X <- X W, Y <- Y W for the 64-column panels.  One persistent CTA of 16 warps per SM walks the flat list
 // of 128-row x 64-column tiles of the block pairs that rotated; tiles arrive through a 2-stage cp.async
 // pipeline (1 KiB contiguous per pair of warps); W (64 x 64) sits in shared memory and feeds the DMMA
-// B-fragments, each fragment serving the two 8-row halves of the warp's 16 rows.
+// B-fragments.  Warp w owns rows 16 (w & 7) .. +15 of the tile and output columns 32 (w >> 3) .. +31: each
+// B-fragment serves the two 8-row halves, and 16 warps per SM keep the FP64 tensor pipe fed (with 8 warps
+// the same kernel ran at 42 % of the DMMA issue peak: the pipe needs ~4 warps per scheduler).
 // ------------------------------------------------------------------------------------------------
 static constexpr int kU32Rows = 128;
 static constexpr int kU32Stride = kU32Rows + 4;
 static constexpr int kU32TileDoubles = kD64 * kU32Stride;
 static constexpr int kU32WStride = kD64 + 4;
+static constexpr int kU32Threads = 512;
 static constexpr size_t kU32Smem = sizeof(double) * (2 * kU32TileDoubles + kD64 * kU32WStride);
 
-__global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a, const unsigned k,
-                                                             const double *__restrict__ wbuf,
-                                                             const int *__restrict__ wflag, const unsigned pairs,
-                                                             unsigned long long *__restrict__ active_out) {
+__global__ void __launch_bounds__(kU32Threads, 1) blk32_update_kernel(const BlockArgs a, const unsigned k,
+                                                                     const double *__restrict__ wbuf,
+                                                                     const int *__restrict__ wflag,
+                                                                     const unsigned pairs,
+                                                                     unsigned long long *__restrict__ active_out) {
   extern __shared__ __align__(16) double sm[];
   double *tiles = sm;                          // 2 stages
   double *Wsm = sm + 2 * kU32TileDoubles;      // Wsm[c * kU32WStride + k] = W[k][c]
@@ -363,11 +367,12 @@ __global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a,
     const Pair bp = block_pair(a, k, active[ap]);
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
-    const unsigned row = (isa ? t : t - tpa) * kU32Rows + 2 * (32 * (warp & 1) + lane);
-    double *dst = tiles + stage * kU32TileDoubles + 2 * (32 * (warp & 1) + lane);
-#pragma unroll 4
-    for (int i = 0; i < 16; ++i) {
-      const unsigned slot = (warp >> 1) + 4 * i;
+    const unsigned rin = 2 * (threadIdx.x & 63);  // 64 threads cover the 128 rows of one column
+    const unsigned row = (isa ? t : t - tpa) * kU32Rows + rin;
+    double *dst = tiles + stage * kU32TileDoubles + rin;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const unsigned slot = (threadIdx.x >> 6) + 8 * i;
       const unsigned col = slot_col32(bp.p, bp.q, slot, a.n);
       int bytes = 0;
       const double *src = a.A;
@@ -384,6 +389,7 @@ __global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a,
   ++issued;
   cp_async_commit();
 
+  const unsigned rowgroup = warp & 7, nhalf = warp >> 3;
   Pair cur_bp = {0u, 0u};
   unsigned cur_pair = 0xffffffffu;
   for (unsigned tau = t0; tau < t1; ++tau) {
@@ -401,30 +407,26 @@ __global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a,
       cur_pair = pr;
       cur_bp = block_pair(a, k, pr);
       const double *w = wbuf + (size_t)pr * kD64 * kD64;
-      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += 256) Wsm[(i >> 6) * kU32WStride + (i & 63)] = w[i];
+      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) Wsm[(i >> 6) * kU32WStride + (i & 63)] = w[i];
       __syncthreads();
     }
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
-    const unsigned row0 = (isa ? t : t - tpa) * kU32Rows + 16 * warp;
-    const double *tile = tiles + ((tau - t0) & 1) * kU32TileDoubles + 16 * warp + g;
-    double af[2][16];
+    const unsigned row0 = (isa ? t : t - tpa) * kU32Rows + 16 * rowgroup;
+    const double *tile = tiles + ((tau - t0) & 1) * kU32TileDoubles + 16 * rowgroup + g;
+    double d[2][4][2];
 #pragma unroll
+    for (int nt = 0; nt < 4; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
+    const double *wl = Wsm + (32 * nhalf + g) * kU32WStride + tg;
+#pragma unroll 4
     for (int ks = 0; ks < 16; ++ks) {
-      af[0][ks] = tile[(4 * ks + tg) * kU32Stride];
-      af[1][ks] = tile[(4 * ks + tg) * kU32Stride + 8];
-    }
-    double d[2][8][2];
+      const double a0 = tile[(4 * ks + tg) * kU32Stride];
+      const double a1 = tile[(4 * ks + tg) * kU32Stride + 8];
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
-    const double *wl = Wsm + g * kU32WStride + tg;
-#pragma unroll
-    for (int ks = 0; ks < 16; ++ks) {
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
+      for (int nt = 0; nt < 4; ++nt) {
         const double bf = wl[(8 * nt) * kU32WStride + 4 * ks];
-        dmma884(d[0][nt][0], d[0][nt][1], af[0][ks], bf);
-        dmma884(d[1][nt][0], d[1][nt][1], af[1][ks], bf);
+        dmma884(d[0][nt][0], d[0][nt][1], a0, bf);
+        dmma884(d[1][nt][0], d[1][nt][1], a1, bf);
       }
     }
 #pragma unroll
@@ -432,9 +434,10 @@ __global__ void __launch_bounds__(256, 1) blk32_update_kernel(const BlockArgs a,
       const unsigned row = row0 + 8 * h + g;
       if (row < limit) {
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) {
-          const unsigned c0 = slot_col32(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg, a.n);
-          const unsigned c1 = slot_col32(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg + 1, a.n);
+        for (int nt = 0; nt < 4; ++nt) {
+          const unsigned s0 = 32 * nhalf + 8 * nt + 2 * tg;
+          const unsigned c0 = slot_col32(cur_bp.p, cur_bp.q, s0, a.n);
+          const unsigned c1 = slot_col32(cur_bp.p, cur_bp.q, s0 + 1, a.n);
           if (c0 != kNoCol) col_ptr_store(a, isa, c0)[row] = d[h][nt][0];
           if (c1 != kNoCol) col_ptr_store(a, isa, c1)[row] = d[h][nt][1];
         }
@@ -505,7 +508,7 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   blk32_gram_kernel<<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
   blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
   if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  blk32_update_kernel<<<sm_count, 256, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
+  blk32_update_kernel<<<sm_count, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
   if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());

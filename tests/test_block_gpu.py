@@ -123,8 +123,10 @@ def test_block_full_size_4096_properties(svdj):
     st = svdj.dgesvd_device(0, 0, n, n, dA.data_ptr(), n, ds.data_ptr(), dV.data_ptr(), n,
                             svdj.default_opts(variant=svdj.VARIANT_BLOCK))
     assert st.converged == 1 and st.sweeps <= 25
-    ref = torch.linalg.svdvals(dA0.T)
-    assert float((ds - ref).abs().max() / ref[0]) <= 1e-12
+    # host LAPACK (numpy, dgesdd) is the yardstick: cuSOLVER's own singular values are 8.6e-13 off at this size
+    # (tools/sigma_check.py), ours agree with LAPACK to ~2e-15
+    ref = np.linalg.svd(A0, compute_uv=False)
+    assert H.sigma_error_normwise(ds.cpu().numpy(), ref) <= 1e-13
     U, V = dA.T, dV.T
     eye = torch.eye(n, dtype=torch.float64, device="cuda")
     bound = 10 * n * H.EPS
