@@ -366,24 +366,41 @@ def run_svdj(args):
     sweep_s = float(np.mean([s_.seconds_sweeps for s_ in stats]))
     peak, peak_src = peaks()
     if last.variant == svdj.VARIANT_BLOCK:
-        # block path: the update kernel X <- X W, Y <- Y W (HBM-bound; ~60 % of the step).  Every 8th launch is
-        # bracketed by events; each block pair it updates reads and writes 32 columns of A and V once:
-        # 2 * 32 * (m + n) * 8 = 512 (m + n) algorithmic bytes.
+        # block path: the update kernel X <- X W, Y <- Y W is the dominant kernel (~55-60 % of a step).  Every 8th
+        # launch is bracketed by CUDA events inside the library; the probes also count the block pairs updated.
+        width = last.reserved or 16          # columns per block: 16 or 32
+        d = 2 * width                        # columns of a block pair
         launches = sum(s_.step_kernel_launches for s_ in stats)
         pairs_upd = sum(s_.probe_block_pairs for s_ in stats)
         k_ms = float(np.mean([s_.step_kernel_ms for s_ in stats]))
-        bytes_per_launch = pairs_upd * 512.0 * (m + n) / max(launches, 1)
-        achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-        ncu_traffic = 484.7e6  # dram read+write per launch, profiles/r1_block_4096.md (4096^2, all pairs active)
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": ncu_traffic if (m, n) == (4096, 4096) else None, "peak_source": peak_src,
-                    "kernel": "blk_update_staged_kernel (X<-XW, Y<-YW; FP64 DMMA tiles, cp.async staged)",
-                    "frac_of_8TBps_nominal": achieved / 8000.0, "alg_bytes_per_launch": bytes_per_launch,
-                    "avg_launch_us": k_ms * 1e3, "launches_probed": int(launches),
-                    "fp64_tensor": {"flops_per_launch": pairs_upd * 2.0 * (m + n) * 1024 / max(launches, 1),
-                                    "achieved_tflops": pairs_upd * 2.0 * (m + n) * 1024 / max(launches, 1) /
-                                    (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0,
-                                    "peak_tflops": 36.9, "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md"}}
+        # per updated block pair: d columns of A and V read once and written once, 2 (m+n) d^2 flops
+        bytes_per_launch = pairs_upd * 16.0 * d * (m + n) / max(launches, 1)
+        flops_per_launch = pairs_upd * 2.0 * (m + n) * d * d / max(launches, 1)
+        gbs = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+        tfs = flops_per_launch / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
+        dmma_peak = 36.9  # TFLOP/s, mma.sync.m8n8k4.f64 issue peak measured on this pool (profiles/r1_fp64_peaks.md)
+        full = (m, n) == (4096, 4096)
+        if width == 32:
+            # 0.31 * 32 = 10 flop/B against a ridge of 36.9 TF / 6.45 TB/s = 5.7: the FP64 tensor pipe bounds it
+            roofline = {"bound": "tensor", "achieved": tfs, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tfs / dmma_peak,
+                        "traffic": 486.6e6 if full else None,
+                        "peak_source": "measured DMMA (mma.sync.m8n8k4.f64) issue peak on this pool, tools/fp64_peak.cu; "
+                                       "MEASURED_PEAKS.json has no FP64 figure (cuBLAS DGEMM here: 35.5)",
+                        "kernel": "blk32_update_kernel (X<-XW, Y<-YW for 64-column block pairs; FP64 DMMA tiles, "
+                                  "W in shared memory, cp.async staged)",
+                        "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
+                        "launches_probed": int(launches),
+                        "hbm": {"alg_bytes_per_launch": bytes_per_launch, "achieved_gbs": gbs, "peak_gbs": peak,
+                                "frac": gbs / peak, "peak_source": peak_src}}
+        else:
+            roofline = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                        "traffic": 484.7e6 if full else None, "peak_source": peak_src,
+                        "kernel": "blk_update_staged_kernel (X<-XW, Y<-YW; FP64 DMMA tiles, cp.async staged)",
+                        "frac_of_8TBps_nominal": gbs / 8000.0, "alg_bytes_per_launch": bytes_per_launch,
+                        "avg_launch_us": k_ms * 1e3, "launches_probed": int(launches),
+                        "fp64_tensor": {"flops_per_launch": flops_per_launch, "achieved_tflops": tfs,
+                                        "peak_tflops": dmma_peak,
+                                        "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md"}}
     else:
         # level-1 path: the fused Gram + rotation step is the only kernel of the sweep loop
         alg_bytes = float(np.mean([algorithmic_bytes(m, n, s_.tested, s_.applied) for s_ in stats]))
@@ -438,6 +455,7 @@ def run_svdj(args):
             "scaling": "strong" if world == 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence",
                        "variant": {1: "level1", 2: "block"}.get(last.variant, str(last.variant)),
+                       "block_width": int(last.reserved) if last.variant == svdj.VARIANT_BLOCK else None,
                        "tol": "m*2^-53 relative", "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20)
                        if 2 * m * n * 8 > 126e6 else "inputs fit L2; restored from a master copy each step",
                        "parallelism": "1 GPU" if world == 1 else f"{world} independent replicas"},
