@@ -64,7 +64,7 @@ typedef struct svdj_opts {
   int sort_desc;      /* 1: sigma descending, U/V columns permuted alike (default); 0: reference's raw column order */
   int variant;        /* SVDJ_VARIANT_* */
   int threshold_mode; /* SVDJ_THRESH_* */
-  int block;          /* block width for SVDJ_VARIANT_BLOCK; 0 = default */
+  int block;          /* column-block width of SVDJ_VARIANT_BLOCK: 16 or 32; 0 = library decides (32 from n = 4096) */
   int device;         /* CUDA device ordinal; < 0 = the calling thread's current device */
   int use_graph;      /* 1: replay each sweep from a CUDA graph; 0: plain launches; < 0: library decides */
 } svdj_opts;
@@ -73,7 +73,7 @@ typedef struct svdj_stats {
   int sweeps;                    /* sweeps executed */
   int converged;                 /* 1 if the last sweep rotated nothing (REL mode) */
   int variant;                   /* variant that ran */
-  int reserved;
+  int reserved;                  /* block path: the column-block width that ran (16 or 32) */
   unsigned long long tested;     /* column pairs whose Gram triple was evaluated */
   unsigned long long applied;    /* column pairs rotated */
   unsigned long long launches;   /* kernels launched by this call */
@@ -208,6 +208,12 @@ size_t svdj_num_steps(size_t n);
 /* Host-side copy of the schedule the kernels use: writes the n/2 pairs (p,q), 0-based, of `step`
  * into pq[0..2*(n/2)) and returns their count (main.cu:526-545, 971-990). */
 size_t svdj_schedule_step(size_t n, size_t step, size_t *pq);
+
+/* The solver keeps its work buffers (device and pinned) in a process-wide pool between calls, because
+ * cudaMalloc / cudaFree synchronise the whole device and showed up as 100 ms stalls inside solves; the
+ * reference allocates and frees its staging vectors on every call (main.cu:484-494, 1385-1392).
+ * svdj_release_workspace() returns every idle pooled buffer to the driver. */
+int svdj_release_workspace(void);
 
 /* Text of the most recent error on the calling thread ("" if none). */
 const char *svdj_last_error(void);

@@ -93,6 +93,7 @@ EXPORTS = (
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_last_error",
+    "svdj_release_workspace",
     "svdj_version",
 )
 
@@ -141,6 +142,8 @@ def _load() -> C.CDLL:
     lib.svdj_num_steps.restype = sz
     lib.svdj_schedule_step.argtypes = [sz, sz, C.POINTER(C.c_size_t)]
     lib.svdj_schedule_step.restype = sz
+    lib.svdj_release_workspace.argtypes = []
+    lib.svdj_release_workspace.restype = i
     lib.svdj_last_error.argtypes = []
     lib.svdj_last_error.restype = C.c_char_p
     lib.svdj_version.argtypes = []
