@@ -318,14 +318,15 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
 // B-fragment serves the two 8-row halves, and 16 warps per SM keep the FP64 tensor pipe fed (with 8 warps
 // the same kernel ran at 42 % of the DMMA issue peak: the pipe needs ~4 warps per scheduler).
 // ------------------------------------------------------------------------------------------------
-static constexpr int kU32Rows = 128;
+static constexpr int kU32Rows = 64;
 static constexpr int kU32Stride = kU32Rows + 4;
 static constexpr int kU32TileDoubles = kD64 * kU32Stride;
 static constexpr int kU32WStride = kD64 + 4;
-static constexpr int kU32Threads = 512;
+static constexpr int kU32Threads = 256;      // 8 warps: 4 row groups of 16 rows x 2 halves of the output columns
+static constexpr int kU32CtasPerSm = 2;      // two independent CTAs per SM: their barriers and tile waits interleave
 static constexpr size_t kU32Smem = sizeof(double) * (2 * kU32TileDoubles + kD64 * kU32WStride);
 
-__global__ void __launch_bounds__(kU32Threads, 1) blk32_update_kernel(const BlockArgs a, const unsigned k,
+__global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kernel(const BlockArgs a, const unsigned k,
                                                                      const double *__restrict__ wbuf,
                                                                      const int *__restrict__ wflag,
                                                                      const unsigned pairs,
@@ -367,12 +368,12 @@ __global__ void __launch_bounds__(kU32Threads, 1) blk32_update_kernel(const Bloc
     const Pair bp = block_pair(a, k, active[ap]);
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
-    const unsigned rin = 2 * (threadIdx.x & 63);  // 64 threads cover the 128 rows of one column
+    const unsigned rin = 2 * lane;  // one warp covers the 64 rows of one column (512 contiguous bytes)
     const unsigned row = (isa ? t : t - tpa) * kU32Rows + rin;
     double *dst = tiles + stage * kU32TileDoubles + rin;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const unsigned slot = (threadIdx.x >> 6) + 8 * i;
+      const unsigned slot = warp + 8 * i;
       const unsigned col = slot_col32(bp.p, bp.q, slot, a.n);
       int bytes = 0;
       const double *src = a.A;
@@ -389,7 +390,7 @@ __global__ void __launch_bounds__(kU32Threads, 1) blk32_update_kernel(const Bloc
   ++issued;
   cp_async_commit();
 
-  const unsigned rowgroup = warp & 7, nhalf = warp >> 3;
+  const unsigned rowgroup = warp & 3, nhalf = warp >> 2;
   Pair cur_bp = {0u, 0u};
   unsigned cur_pair = 0xffffffffu;
   for (unsigned tau = t0; tau < t1; ++tau) {
@@ -508,7 +509,7 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   blk32_gram_kernel<<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
   blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
   if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  blk32_update_kernel<<<sm_count, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
+  blk32_update_kernel<<<sm_count * kU32CtasPerSm, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
   if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());
