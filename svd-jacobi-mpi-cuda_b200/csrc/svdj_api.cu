@@ -291,6 +291,19 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   b.split = (unsigned)n;
   b.sched = 0;
   b.sort_cols = 1;
+  b.vranks = 1;
+  // two-level tournament ordering (the ring's ordering with virtual ranks) when the blocks divide evenly
+  if (block && n % (wide ? 32 : 16) == 0) {
+    // P = 4 virtual ranks where the blocks divide evenly (measured best of 1, 2, 4, 16 at 1024..4096), else 2,
+    // else the flat ordering; SVDJ_VRANKS overrides (0 = flat)
+    int P = (nb % 8u == 0) ? 4 : (nb % 4u == 0) ? 2 : 0;
+    if (const char *env = std::getenv("SVDJ_VRANKS")) P = std::atoi(env);
+    if (P >= 2 && nb % (2u * (unsigned)P) == 0 && nb >= 4) {
+      b.sched = 2;
+      b.vranks = P;
+      if (const char *e2 = std::getenv("SVDJ_SORT")) b.sort_cols = std::atoi(e2);
+    }
+  }
   b.tol = o.tol;
   b.threshold_mode = o.threshold_mode;
   // One cyclic sweep of the small eigen-solve per visit below n = 8192, two from there on: a converged inner

@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
   // addresses are (stride - 1) p + const; an odd (stride - 1) spreads them over the banks (stride kD + 1 put
   // all sixteen pairs on one bank), and the diagonal, (stride + 1) p, stays conflict-free as well.
   __shared__ double Gb[2][kD][kD + 2];
-  __shared__ double W[kD][kD + 2];
+  __shared__ double Wb[2][kD][kD + 2];
   __shared__ double T[kD][kD + 2];
   __shared__ unsigned long long fresh_max;
   __shared__ int rank_of[kD];
@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     Gb[0][r][c] = s;
     if (ti != tj) Gb[0][c][r] = s;
   }
-  for (unsigned i = tid; i < kD * kD; i += 256) W[i >> 5][i & 31] = ((i >> 5) == (i & 31)) ? 1.0 : 0.0;
+  for (unsigned i = tid; i < kD * kD; i += 256) Wb[0][i >> 5][i & 31] = ((i >> 5) == (i & 31)) ? 1.0 : 0.0;
   if (tid == 0) fresh_max = 0ull;
   __syncthreads();
 
@@ -172,55 +172,76 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
     if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(mx));
   }
 
+  // Systolic layout: rows and columns of G (and the columns of W) are kept in SLOT order.  Slot j and slot
+  // 16 + j always hold the two indices of pair j, so thread (j1, j2) always works on G[{j1, 16+j1}][{j2, 16+j2}]:
+  // fixed, conflict-free addresses (indexing by the circle-method indices themselves put the sixteen rotation
+  // inputs of a step on one bank).  The round-robin move of the indices is folded into the write-back: every
+  // updated value goes to the slot its index occupies in the next step, in the other buffer; after a whole
+  // sweep every index is back in its own slot, so slot order = index order at sweep boundaries.
+  // FULL schedule: all 496 pairs in 31 steps (top 0 stays, top j -> top j+1, top 15 -> bottom 15, bottom j ->
+  // bottom j-1, bottom 0 -> top 1).  CROSS: the 256 pairs with one index in each column block, 16 steps (bottom
+  // slots rotate, top slots stay) -- used after the first step of a sweep, so that a column pair is rotated once
+  // per sweep as in the reference's ordering, not re-rotated with its own block in every step.
+  const bool cross = a.cross_only != 0;
+  const int nsteps = cross ? kBW : kD - 1;
+  auto next_slot = [cross](int p) {
+    if (cross) return p < kBW ? p : kBW + ((p - kBW + kBW - 1) & (kBW - 1));
+    return p == 0 ? 0 : (p < kBW - 1 ? p + 1 : (p == kBW - 1 ? kD - 1 : (p == kBW ? 1 : p - 1)));
+  };
   int total_rot = 0;
   int cur = 0;
   const int j1 = tid >> 4, j2 = tid & 15;
   const double tol2 = a.tol * a.tol;
-  for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+  const int nr_t = next_slot(j1), nr_b = next_slot(kBW + j1), nc_t = next_slot(j2), nc_b = next_slot(kBW + j2);
+  int any = 0;  // anything to rotate among the pairs this schedule visits?  (same test as the steps)
+  for (unsigned i = tid; i < kD * kD; i += 256) {
+    const int r = i >> 5, c = i & 31;
+    if (r < c && (!cross || (r < kBW && c >= kBW))) {
+      const double al = Gb[0][r][c], be = Gb[0][r][r], ga = Gb[0][c][c];
+      any |= (al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2) ? 1 : 0;
+    }
+  }
+  any = __syncthreads_or(any);
+  for (int sw = 0; sw < (any ? a.max_inner_sweeps : 0); ++sw) {
     int sweep_rot = 0;
-    for (int t = 0; t < kD - 1; ++t) {
-      // the step's 16 rotations, computed by every warp (lane & 15 = pair index).  All eleven shared-memory
-      // loads of the step are issued before the rotation arithmetic so that their latency hides behind it.
-      int p2, q2, p1, q1;
-      circle_pair(t, j2, p2, q2);
-      circle_pair(t, j1, p1, q1);
-      const double al = Gb[cur][p2][q2], be = Gb[cur][p2][p2], ga = Gb[cur][q2][q2];
-      const double g11 = Gb[cur][p1][p2], g12 = Gb[cur][p1][q2], g21 = Gb[cur][q1][p2], g22 = Gb[cur][q1][q2];
-      const double wp0 = W[j1][p2], wq0 = W[j1][q2], wp1 = W[j1 + 16][p2], wq1 = W[j1 + 16][q2];
+    for (int t = 0; t < nsteps; ++t) {
+      // the step's 16 rotations, computed by every warp (lane & 15 = pair index); all loads first
+      const double al = Gb[cur][j2][kBW + j2], be = Gb[cur][j2][j2], ga = Gb[cur][kBW + j2][kBW + j2];
+      const double g11 = Gb[cur][j1][j2], g12 = Gb[cur][j1][kBW + j2];
+      const double g21 = Gb[cur][kBW + j1][j2], g22 = Gb[cur][kBW + j1][kBW + j2];
+      const double wp0 = Wb[cur][j1][j2], wq0 = Wb[cur][j1][kBW + j2];
+      const double wp1 = Wb[cur][j1 + 16][j2], wq1 = Wb[cur][j1 + 16][kBW + j2];
       // |alpha| > tol sqrt(beta gamma) (lib/JacobiMethods.cu:462/466), and neither column numerically zero
       const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
       double c2 = 1.0, s2 = 0.0;
       if (rot) fast_rotation(al, be, ga, c2, s2);
-      const unsigned mask = __ballot_sync(0xffffffffu, rot) & 0xffffu;
-      if (mask == 0u) continue;  // every warp sees the same 16 decisions: uniform across the CTA
-      sweep_rot += __popc(mask);
+      sweep_rot += __popc(__ballot_sync(0xffffffffu, rot) & 0xffffu);
       const double c1 = __shfl_sync(0xffffffffu, c2, j1), s1 = __shfl_sync(0xffffffffu, s2, j1);
-      {
-        // columns: col_p' = c col_p - s col_q, col_q' = s col_p + c col_q (the kernel at :1483-1491)
-        const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
-        const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
-        // rows: the transpose of the same rotation
-        double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
-        double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
-        if (j1 == j2 && s1 != 0.0) {
-          n12 = 0.0;  // the rotated pair is orthogonal by construction
-          n21 = 0.0;
-        }
-        Gb[cur ^ 1][p1][p2] = n11;
-        Gb[cur ^ 1][p1][q2] = n12;
-        Gb[cur ^ 1][q1][p2] = n21;
-        Gb[cur ^ 1][q1][q2] = n22;
-        W[j1][p2] = c2 * wp0 - s2 * wq0;  // rows j1 and j1 + 16 of W, pair j2
-        W[j1][q2] = s2 * wp0 + c2 * wq0;
-        W[j1 + 16][p2] = c2 * wp1 - s2 * wq1;
-        W[j1 + 16][q2] = s2 * wp1 + c2 * wq1;
+      // columns: col_p' = c col_p - s col_q, col_q' = s col_p + c col_q (the kernel at :1483-1491)
+      const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
+      const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
+      // rows: the transpose of the same rotation
+      double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
+      double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
+      if (j1 == j2 && s1 != 0.0) {
+        n12 = 0.0;  // the rotated pair is orthogonal by construction
+        n21 = 0.0;
       }
+      Gb[cur ^ 1][nr_t][nc_t] = n11;
+      Gb[cur ^ 1][nr_t][nc_b] = n12;
+      Gb[cur ^ 1][nr_b][nc_t] = n21;
+      Gb[cur ^ 1][nr_b][nc_b] = n22;
+      Wb[cur ^ 1][j1][nc_t] = c2 * wp0 - s2 * wq0;  // rows j1 and j1 + 16 of W, pair j2
+      Wb[cur ^ 1][j1][nc_b] = s2 * wp0 + c2 * wq0;
+      Wb[cur ^ 1][j1 + 16][nc_t] = c2 * wp1 - s2 * wq1;
+      Wb[cur ^ 1][j1 + 16][nc_b] = s2 * wp1 + c2 * wq1;
       cur ^= 1;
       __syncthreads();
     }
     total_rot += sweep_rot;
     if (sweep_rot == 0) break;
   }
+  double(*W)[kD + 2] = Wb[cur];  // the live copy
 
   if (total_rot > 0 || a.force_update) {
     // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  thread (r = tid>>3, c4 = (tid&7)*4) computes 4 entries
@@ -606,6 +627,12 @@ static bool blk_force_plain_update() {
   return e != nullptr && e[0] == '1';
 }
 
+// flat ordering (sched 0): full eigen-solve in every step unless SVDJ_CROSS_FLAT=1 (it needs fewer sweeps that way)
+static bool blk_cross_flat() {
+  const char *e = std::getenv("SVDJ_CROSS_FLAT");
+  return e != nullptr && e[0] == '1';
+}
+
 unsigned blk_num_blocks(size_t n) { return (unsigned)((n + kBW - 1) / kBW); }
 
 static unsigned gram_splits(size_t m, unsigned pairs) {
@@ -649,6 +676,14 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
     a.A2_st = (a_in.A2_st ? a_in.A2_st : a_in.A2) - (size_t)a.split * a.lda;
     double *v2 = a_in.V2_st ? a_in.V2_st : a_in.V2;
     a.V2_st = v2 ? v2 - (size_t)a.split * a.ldv : nullptr;
+  }
+  // first step of a phase or sweep: full eigen-solve (every block sits in exactly one pair when their number is
+  // even); afterwards only the cross pairs.  The bipartite schedule of the ring's CROSS phase never needs the
+  // intra-block pairs (its blocks were swept internally in the round before).
+  {
+    const char *e = std::getenv("SVDJ_FULL_INNER");
+    const bool always_full = e != nullptr && e[0] == '1';
+    a.cross_only = (!always_full && (a.sched == 1 || (k > 1 && a.nb % 2 == 0 && (a.sched == 2 || blk_cross_flat())))) ? 1 : 0;
   }
   const unsigned splits = gram_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
 // its 32 lanes (lane = pair index) and fetches its own row rotation by shuffle; one barrier per step.
 // ------------------------------------------------------------------------------------------------
 static constexpr int kE32Stride = kD64 + 2;  // odd (stride - 1): conflict-free rotation inputs, see svdj_block.cu
-static constexpr size_t kE32Smem = sizeof(double) * 4 * kD64 * kE32Stride;
+static constexpr size_t kE32Smem = sizeof(double) * 5 * kD64 * kE32Stride;
 
 __device__ __forceinline__ void circle_pair64(int t, int j, int &p, int &q) {
   int x, y;
@@ -155,9 +155,12 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   double(*G1)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + kD64 * kE32Stride);
   double(*W)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + 2 * kD64 * kE32Stride);
   double(*T)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + 3 * kD64 * kE32Stride);
+  double(*W1)[kE32Stride] = reinterpret_cast<double(*)[kE32Stride]>(sm + 4 * kD64 * kE32Stride);
   __shared__ unsigned long long fresh_max;
   __shared__ int rank_of[kD64];
   __shared__ int valid[kD64];
+  __shared__ double rot_c[32], rot_s[32];
+  __shared__ int sweep_rot_s;
   const unsigned tid = threadIdx.x, lane = tid & 31;
   const unsigned pair = blockIdx.x;
 
@@ -196,49 +199,89 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(mx));
   }
 
+  // Systolic layout.  Rows and columns of G (and the columns of W) are kept in SLOT order: slot j and slot 32 + j
+  // always hold the two indices of pair j, so thread (warp w, lane l) always works on G[{w, 32+w}][{l, 32+l}] --
+  // fixed, conflict-free addresses (with the circle-method indices themselves half of all shared-memory
+  // wavefronts were bank conflicts).  The round-robin move of the indices is folded into the write-back: each
+  // updated value is stored at the slot its index occupies in the next step (top 0 stays, top j -> top j+1,
+  // top 31 -> bottom 31, bottom j -> bottom j-1, bottom 0 -> top 1), into the other buffer.  After the 63 steps
+  // of a sweep every index is back in its slot, so slot order = index order at every sweep boundary.
+  // Two schedules.  FULL: all 2016 pairs of the 64 indices in 63 steps (circle method).  CROSS: only the 1024
+  // pairs with one index in each column block, in 32 steps (the bottom slots rotate, the top slots stay).  A
+  // sweep uses FULL for its first step, which orthogonalises every block internally, and CROSS afterwards:
+  // every column pair is then rotated once per sweep, as in the reference's ordering, instead of re-rotating
+  // the 992 intra-block pairs in each of the sweep's steps.
+  const bool cross = a.cross_only != 0;
+  const int nsteps = cross ? 32 : kD64 - 1;
+  auto next_slot = [cross](int p) {
+    if (cross) return p < 32 ? p : 32 + ((p - 32 + 31) & 31);
+    return p == 0 ? 0 : (p < 31 ? p + 1 : (p == 31 ? 63 : (p == 32 ? 1 : p - 1)));
+  };
   int total_rot = 0;
   int cur = 0;
-  const int j1 = tid >> 5, j2 = lane;
+  const int w1 = tid >> 5, l2 = lane;
   const double tol2 = a.tol * a.tol;
-  for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
-    int sweep_rot = 0;
-    for (int t = 0; t < kD64 - 1; ++t) {
+  const int nr_t = next_slot(w1), nr_b = next_slot(32 + w1), nc_t = next_slot(l2), nc_b = next_slot(32 + l2);
+  // anything to do at all?  (the same test the steps apply, on the fresh matrix)
+  int any = 0;
+  for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
+    const int r = i >> 6, c = i & 63;
+    if (r < c && (!cross || (r < 32 && c >= 32))) {  // only the pairs this schedule visits
+      const double al = G0[r][c], be = G0[r][r], ga = G0[c][c];
+      any |= (al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2) ? 1 : 0;
+    }
+  }
+  any = __syncthreads_or(any);
+  for (int sw = 0; sw < (any ? a.max_inner_sweeps : 0); ++sw) {
+    int sweep_rot = 0;  // counted by warp 0
+    for (int t = 0; t < nsteps; ++t) {
       double(*Gc)[kE32Stride] = cur ? G1 : G0;
       double(*Gn)[kE32Stride] = cur ? G0 : G1;
-      int p2, q2, p1, q1;
-      circle_pair64(t, j2, p2, q2);
-      circle_pair64(t, j1, p1, q1);
-      const double al = Gc[p2][q2], be = Gc[p2][p2], ga = Gc[q2][q2];
-      const double g11 = Gc[p1][p2], g12 = Gc[p1][q2], g21 = Gc[q1][p2], g22 = Gc[q1][q2];
-      const double wp0 = W[j1][p2], wq0 = W[j1][q2], wp1 = W[j1 + 32][p2], wq1 = W[j1 + 32][q2];
-      const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
-      double c2 = 1.0, s2 = 0.0;
-      if (rot) fast_rotation(al, be, ga, c2, s2);
-      const unsigned mask = __ballot_sync(0xffffffffu, rot);
-      if (mask == 0u) continue;  // every warp sees the same 32 decisions
-      sweep_rot += __popc(mask);
-      const double c1 = __shfl_sync(0xffffffffu, c2, j1), s1 = __shfl_sync(0xffffffffu, s2, j1);
+      double(*Wc)[kE32Stride] = cur ? W1 : W;
+      double(*Wn)[kE32Stride] = cur ? W : W1;
+      const double g11 = Gc[w1][l2], g12 = Gc[w1][32 + l2], g21 = Gc[32 + w1][l2], g22 = Gc[32 + w1][32 + l2];
+      const double wp0 = Wc[w1][l2], wq0 = Wc[w1][32 + l2], wp1 = Wc[w1 + 32][l2], wq1 = Wc[w1 + 32][32 + l2];
+      if (w1 == 0) {
+        // the 32 rotations of the step, once per CTA (one per lane); with every warp computing them the kernel
+        // was bound by instruction issue and the FP64 pipe (~half of its instructions were this arithmetic)
+        const double al = Gc[l2][32 + l2], be = Gc[l2][l2], ga = Gc[32 + l2][32 + l2];
+        const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
+        double c = 1.0, sn = 0.0;
+        if (rot) fast_rotation(al, be, ga, c, sn);
+        rot_c[l2] = c;
+        rot_s[l2] = sn;
+        sweep_rot += __popc(__ballot_sync(0xffffffffu, rot));
+      }
+      __syncthreads();
+      const double c2 = rot_c[l2], s2 = rot_s[l2], c1 = rot_c[w1], s1 = rot_s[w1];
       const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
       const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
       double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
       double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
-      if (j1 == j2 && s1 != 0.0) {
-        n12 = 0.0;
+      if (w1 == l2 && s1 != 0.0) {
+        n12 = 0.0;  // the rotated pair is orthogonal by construction
         n21 = 0.0;
       }
-      Gn[p1][p2] = n11;
-      Gn[p1][q2] = n12;
-      Gn[q1][p2] = n21;
-      Gn[q1][q2] = n22;
-      W[j1][p2] = c2 * wp0 - s2 * wq0;
-      W[j1][q2] = s2 * wp0 + c2 * wq0;
-      W[j1 + 32][p2] = c2 * wp1 - s2 * wq1;
-      W[j1 + 32][q2] = s2 * wp1 + c2 * wq1;
+      Gn[nr_t][nc_t] = n11;
+      Gn[nr_t][nc_b] = n12;
+      Gn[nr_b][nc_t] = n21;
+      Gn[nr_b][nc_b] = n22;
+      Wn[w1][nc_t] = c2 * wp0 - s2 * wq0;
+      Wn[w1][nc_b] = s2 * wp0 + c2 * wq0;
+      Wn[w1 + 32][nc_t] = c2 * wp1 - s2 * wq1;
+      Wn[w1 + 32][nc_b] = s2 * wp1 + c2 * wq1;
       cur ^= 1;
       __syncthreads();
     }
-    total_rot += sweep_rot;
-    if (sweep_rot == 0) break;
+    if (tid == 0) sweep_rot_s = sweep_rot;
+    __syncthreads();
+    const int sr = sweep_rot_s;
+    total_rot += sr;
+    if (sr == 0) break;
+  }
+  if (cur) {  // an odd number of steps was taken: the live copies are G1 / W1; bring W back (G is only read)
+    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = W1[i >> 6][i & 63];
+    __syncthreads();
   }
 
   if (total_rot > 0 || a.force_update) {
@@ -408,7 +451,12 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
       cur_pair = pr;
       cur_bp = block_pair(a, k, pr);
       const double *w = wbuf + (size_t)pr * kD64 * kD64;
-      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) Wsm[(i >> 6) * kU32WStride + (i & 63)] = w[i];
+      // fragment-major layout: the four B-fragments (4 output tiles) a lane needs for one k-step sit in 32
+      // contiguous bytes, so two 128-bit loads replace four 64-bit ones and a warp reads 1 KiB without conflicts
+      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) {
+        const unsigned nt = i & 3, ln = (i >> 2) & 31, ks = (i >> 7) & 15, nh = i >> 11;
+        Wsm[i] = w[(32 * nh + 8 * nt + (ln >> 2)) * kD64 + 4 * ks + (ln & 3)];
+      }
       __syncthreads();
     }
     const bool isa = t < tpa;
@@ -418,17 +466,20 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     double d[2][4][2];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
-    const double *wl = Wsm + (32 * nhalf + g) * kU32WStride + tg;
-#pragma unroll 4
+    const double2 *wl = reinterpret_cast<const double2 *>(Wsm + (nhalf * 16 * 32 + lane) * 4);
+#pragma unroll 8
     for (int ks = 0; ks < 16; ++ks) {
       const double a0 = tile[(4 * ks + tg) * kU32Stride];
       const double a1 = tile[(4 * ks + tg) * kU32Stride + 8];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        const double bf = wl[(8 * nt) * kU32WStride + 4 * ks];
-        dmma884(d[0][nt][0], d[0][nt][1], a0, bf);
-        dmma884(d[1][nt][0], d[1][nt][1], a1, bf);
-      }
+      const double2 b01 = wl[ks * 64], b23 = wl[ks * 64 + 1];
+      dmma884(d[0][0][0], d[0][0][1], a0, b01.x);
+      dmma884(d[1][0][0], d[1][0][1], a1, b01.x);
+      dmma884(d[0][1][0], d[0][1][1], a0, b01.y);
+      dmma884(d[1][1][0], d[1][1][1], a1, b01.y);
+      dmma884(d[0][2][0], d[0][2][1], a0, b23.x);
+      dmma884(d[1][2][0], d[1][2][1], a1, b23.x);
+      dmma884(d[0][3][0], d[0][3][1], a0, b23.y);
+      dmma884(d[1][3][0], d[1][3][1], a1, b23.y);
     }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -451,6 +502,11 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+static bool blk_full_inner() {  // SVDJ_FULL_INNER=1: always the full schedule (for comparisons)
+  const char *e = std::getenv("SVDJ_FULL_INNER");
+  return e != nullptr && e[0] == '1';
+}
+
 unsigned blk32_num_blocks(size_t n) { return (unsigned)((n + kB32 - 1) / kB32); }
 
 static unsigned gram32_splits(size_t m, unsigned pairs) {
@@ -488,6 +544,9 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   a.V_st = a.V;
   a.A2_st = a.A;
   a.V2_st = a.V;
+  // first step of a sweep: full eigen-solve (every block is in exactly one pair when their number is even);
+  // later steps: cross pairs only
+  a.cross_only = (k > 1 && (a.nb % 2 == 0) && !blk_full_inner()) ? 1 : 0;  // both orderings (sched 0 and 2)
   static const cudaError_t attrs = [] {
     cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(sizeof(double) * kG32Stages * kG32TileDoubles));

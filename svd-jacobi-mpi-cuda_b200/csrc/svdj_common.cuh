@@ -192,6 +192,8 @@ struct BlockArgs {
   // neighbour GPUs.  force_update makes that step rewrite every block pair, rotated or not.
   double *A_st = nullptr, *A2_st = nullptr, *V_st = nullptr, *V2_st = nullptr;
   int force_update = 0;
+  int vranks = 1;      // sched 2: number of virtual ranks P of the two-level tournament
+  int cross_only = 0;  // eigen-solve visits only the pairs with one column in each block (set per step by the launchers)
   double tol;
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
