@@ -286,26 +286,31 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
 
   if (total_rot > 0 || a.force_update) {
     double(*Gc)[kE32Stride] = cur ? G1 : G0;
-    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W); thread (r = tid >> 4, c0 = (tid & 15) * 4) computes 4 entries
-    const int r = tid >> 4, c0 = (tid & 15) * 4;
-    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-#pragma unroll 8
-    for (int k2 = 0; k2 < kD64; ++k2) {
-      const double wr = W[k2][r];
-      t0 = fma(wr, W[k2][c0 + 0], t0);
-      t1 = fma(wr, W[k2][c0 + 1], t1);
-      t2 = fma(wr, W[k2][c0 + 2], t2);
-      t3 = fma(wr, W[k2][c0 + 3], t3);
+    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  Both 64 x 64 x 64 products run as DMMA tiles: warp w owns the
+    // 8 x 16 piece (tile row w >> 2, tile columns 2 (w & 3), +1) of the result.  (As scalar FMAs they were 45 % of
+    // this kernel's time, bound by the shared-memory loads: 5 loads per 4 FMAs.)
+    const int g = lane >> 2, tg = lane & 3;
+    const int ti = (tid >> 5) >> 2, tj = 2 * ((tid >> 5) & 3);
+    {
+      double d0a = 0.0, d0b = 0.0, d1a = 0.0, d1b = 0.0;
+#pragma unroll 4
+      for (int ks = 0; ks < 16; ++ks) {
+        const double af = W[4 * ks + tg][8 * ti + g];
+        dmma884(d0a, d0b, af, W[4 * ks + tg][8 * tj + g]);
+        dmma884(d1a, d1b, af, W[4 * ks + tg][8 * tj + 8 + g]);
+      }
+      const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
+      T[r][c] = (r == c ? 1.5 : 0.0) - 0.5 * d0a;
+      T[r][c + 1] = (r == c + 1 ? 1.5 : 0.0) - 0.5 * d0b;
+      T[r][c + 8] = (r == c + 8 ? 1.5 : 0.0) - 0.5 * d1a;
+      T[r][c + 9] = (r == c + 9 ? 1.5 : 0.0) - 0.5 * d1b;
     }
-    T[r][c0 + 0] = (r == c0 + 0 ? 1.5 : 0.0) - 0.5 * t0;
-    T[r][c0 + 1] = (r == c0 + 1 ? 1.5 : 0.0) - 0.5 * t1;
-    T[r][c0 + 2] = (r == c0 + 2 ? 1.5 : 0.0) - 0.5 * t2;
-    T[r][c0 + 3] = (r == c0 + 3 ? 1.5 : 0.0) - 0.5 * t3;
     if (tid < kD64) {
       const Pair bp = block_pair(a, k, pair);
       valid[tid] = slot_col32(bp.p, bp.q, tid, a.n) != kNoCol;
     }
     __syncthreads();
+    const int all_valid = __syncthreads_and(tid >= kD64 || valid[tid]);
     if (tid < kD64) {  // output slot of column tid: eigenvalues descending over the valid slots (single GPU only)
       int out = tid;
       if (a.sort_cols && valid[tid]) {
@@ -315,34 +320,36 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
           const double dj = Gc[j][j];
           rk += (valid[j] && (dj > di || (dj == di && j < (int)tid))) ? 1 : 0;
         }
-        int seen = 0;
-        for (int j = 0; j < kD64; ++j) {
-          if (valid[j]) {
-            if (seen == rk) {
-              out = j;
-              break;
+        out = rk;
+        if (!all_valid) {  // ragged last block: the rk-th valid slot
+          int seen = 0;
+          for (int j = 0; j < kD64; ++j) {
+            if (valid[j]) {
+              if (seen == rk) {
+                out = j;
+                break;
+              }
+              ++seen;
             }
-            ++seen;
           }
         }
       }
       rank_of[tid] = out;
     }
     __syncthreads();
-    double u0 = 0, u1 = 0, u2 = 0, u3 = 0;
-#pragma unroll 8
-    for (int k2 = 0; k2 < kD64; ++k2) {
-      const double wr = W[r][k2];
-      u0 = fma(wr, T[k2][c0 + 0], u0);
-      u1 = fma(wr, T[k2][c0 + 1], u1);
-      u2 = fma(wr, T[k2][c0 + 2], u2);
-      u3 = fma(wr, T[k2][c0 + 3], u3);
+    double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
+#pragma unroll 4
+    for (int ks = 0; ks < 16; ++ks) {
+      const double af = W[8 * ti + g][4 * ks + tg];
+      dmma884(u0a, u0b, af, T[4 * ks + tg][8 * tj + g]);
+      dmma884(u1a, u1b, af, T[4 * ks + tg][8 * tj + 8 + g]);
     }
     double *wdst = wbuf + (size_t)pair * kD64 * kD64;  // column-major: wdst[c * 64 + r]
-    wdst[rank_of[c0 + 0] * kD64 + r] = u0;
-    wdst[rank_of[c0 + 1] * kD64 + r] = u1;
-    wdst[rank_of[c0 + 2] * kD64 + r] = u2;
-    wdst[rank_of[c0 + 3] * kD64 + r] = u3;
+    const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
+    wdst[rank_of[c] * kD64 + r] = u0a;
+    wdst[rank_of[c + 1] * kD64 + r] = u0b;
+    wdst[rank_of[c + 8] * kD64 + r] = u1a;
+    wdst[rank_of[c + 9] * kD64 + r] = u1b;
   }
   if (tid == 0) {
     wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;
@@ -379,6 +386,7 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
   double *Wsm = sm + 2 * kU32TileDoubles;      // Wsm[c * kU32WStride + k] = W[k][c]
   __shared__ unsigned short active[kMaxPairs32];
   __shared__ unsigned n_active_s;
+  __shared__ double *coltab[2][4][kD64];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned g = lane >> 2, tg = lane & 3;
 
@@ -406,25 +414,43 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
   const unsigned t1 = (unsigned)(total * (blockIdx.x + 1) / gridDim.x);
   if (t0 >= t1) return;
 
-  auto issue_tile = [&](unsigned tau, int stage) {
-    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+  // Column pointers of a block pair, worked out once per pair (schedule, ragged-block and split/peer selection
+  // are dozens of integer instructions per column; per tile they cost more issue slots than the DMMAs).  Two
+  // sets: the loads run one tile ahead of the arithmetic and may already be in the next pair.
+  auto fill_table = [&](unsigned ap) {
     const Pair bp = block_pair(a, k, active[ap]);
+    const unsigned set = ap & 1u;
+    for (unsigned i = threadIdx.x; i < 4 * kD64; i += kU32Threads) {
+      const unsigned which = i >> 6, slot = i & 63u;  // 0: A load, 1: V load, 2: A store, 3: V store
+      const unsigned col = slot_col32(bp.p, bp.q, slot, a.n);
+      double *ptr = nullptr;
+      if (col != kNoCol) ptr = (which < 2) ? col_ptr(a, which == 0, col) : col_ptr_store(a, which == 2, col);
+      coltab[set][which][slot] = ptr;
+    }
+  };
+
+  unsigned issue_ap = 0xffffffffu, issue_next = 0;  // pair of the tile being issued, first tile of the next pair
+  auto issue_tile = [&](unsigned tau, int stage) {
+    if (tau >= issue_next || issue_ap == 0xffffffffu) {  // CTA-uniform
+      issue_ap = tau / tpp;
+      issue_next = (issue_ap + 1) * tpp;
+      fill_table(issue_ap);
+      __syncthreads();
+    }
+    const unsigned t = tau - issue_ap * tpp;
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned rin = 2 * lane;  // one warp covers the 64 rows of one column (512 contiguous bytes)
     const unsigned row = (isa ? t : t - tpa) * kU32Rows + rin;
     double *dst = tiles + stage * kU32TileDoubles + rin;
+    double *const *tab = coltab[issue_ap & 1u][isa ? 0 : 1];
+    const int rb = (row < limit) ? ((row + 1 < limit) ? 16 : 8) : 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const unsigned slot = warp + 8 * i;
-      const unsigned col = slot_col32(bp.p, bp.q, slot, a.n);
-      int bytes = 0;
-      const double *src = a.A;
-      if (col != kNoCol && row < limit) {
-        bytes = (row + 1 < limit) ? 16 : 8;
-        src = col_ptr(a, isa, col) + row;
-      }
-      cp_async16(dst + slot * kU32Stride, src, bytes);
+      const double *base = tab[slot];
+      const bool ok = base != nullptr && rb != 0;
+      cp_async16(dst + slot * kU32Stride, ok ? base + row : a.A, ok ? rb : 0);
     }
   };
 
@@ -434,8 +460,7 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
   cp_async_commit();
 
   const unsigned rowgroup = warp & 3, nhalf = warp >> 2;
-  Pair cur_bp = {0u, 0u};
-  unsigned cur_pair = 0xffffffffu;
+  unsigned cur_ap = 0xffffffffu, cur_next = 0;
   for (unsigned tau = t0; tau < t1; ++tau) {
     cp_async_wait<0>();
     __syncthreads();  // tile tau has landed; everyone is done with the other stage and with the previous W
@@ -445,20 +470,19 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     }
     cp_async_commit();
 
-    const unsigned ap = tau / tpp, t = tau - ap * tpp;
-    const unsigned pr = active[ap];
-    if (pr != cur_pair) {  // CTA-uniform: a new block pair, load its W
-      cur_pair = pr;
-      cur_bp = block_pair(a, k, pr);
-      const double *w = wbuf + (size_t)pr * kD64 * kD64;
-      // fragment-major layout: the four B-fragments (4 output tiles) a lane needs for one k-step sit in 32
-      // contiguous bytes, so two 128-bit loads replace four 64-bit ones and a warp reads 1 KiB without conflicts
+    if (tau >= cur_next || cur_ap == 0xffffffffu) {  // CTA-uniform: a new block pair, load its W
+      cur_ap = tau / tpp;
+      cur_next = (cur_ap + 1) * tpp;
+      const double *w = wbuf + (size_t)active[cur_ap] * kD64 * kD64;
+      // fragment-major layout: per k-step and half of the output columns, 32 lanes x (b0, b1) then 32 lanes x
+      // (b2, b3): each of the two 128-bit loads of a warp reads 512 contiguous bytes
       for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) {
-        const unsigned nt = i & 3, ln = (i >> 2) & 31, ks = (i >> 7) & 15, nh = i >> 11;
-        Wsm[i] = w[(32 * nh + 8 * nt + (ln >> 2)) * kD64 + 4 * ks + (ln & 3)];
+        const unsigned lo = i & 1, ln = (i >> 1) & 31, hi = (i >> 6) & 1, ks = (i >> 7) & 15, nh = i >> 11;
+        Wsm[i] = w[(32 * nh + 8 * (2 * hi + lo) + (ln >> 2)) * kD64 + 4 * ks + (ln & 3)];
       }
       __syncthreads();
     }
+    const unsigned t = tau - cur_ap * tpp;
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row0 = (isa ? t : t - tpa) * kU32Rows + 16 * rowgroup;
@@ -466,12 +490,12 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     double d[2][4][2];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
-    const double2 *wl = reinterpret_cast<const double2 *>(Wsm + (nhalf * 16 * 32 + lane) * 4);
+    const double2 *wl = reinterpret_cast<const double2 *>(Wsm + nhalf * 16 * 128 + 2 * lane);
 #pragma unroll 8
     for (int ks = 0; ks < 16; ++ks) {
       const double a0 = tile[(4 * ks + tg) * kU32Stride];
       const double a1 = tile[(4 * ks + tg) * kU32Stride + 8];
-      const double2 b01 = wl[ks * 64], b23 = wl[ks * 64 + 1];
+      const double2 b01 = wl[ks * 64], b23 = wl[ks * 64 + 32];
       dmma884(d[0][0][0], d[0][0][1], a0, b01.x);
       dmma884(d[1][0][0], d[1][0][1], a1, b01.x);
       dmma884(d[0][1][0], d[0][1][1], a0, b01.y);
@@ -481,17 +505,16 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
       dmma884(d[0][3][0], d[0][3][1], a0, b23.y);
       dmma884(d[1][3][0], d[1][3][1], a1, b23.y);
     }
+    double *const *stab = coltab[cur_ap & 1u][isa ? 2 : 3] + 32 * nhalf + 2 * tg;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const unsigned row = row0 + 8 * h + g;
-      if (row < limit) {
+    for (int nt = 0; nt < 4; ++nt) {
+      double *const c0 = stab[8 * nt], *const c1 = stab[8 * nt + 1];
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
-          const unsigned s0 = 32 * nhalf + 8 * nt + 2 * tg;
-          const unsigned c0 = slot_col32(cur_bp.p, cur_bp.q, s0, a.n);
-          const unsigned c1 = slot_col32(cur_bp.p, cur_bp.q, s0 + 1, a.n);
-          if (c0 != kNoCol) col_ptr_store(a, isa, c0)[row] = d[h][nt][0];
-          if (c1 != kNoCol) col_ptr_store(a, isa, c1)[row] = d[h][nt][1];
+      for (int h = 0; h < 2; ++h) {
+        const unsigned row = row0 + 8 * h + g;
+        if (row < limit) {
+          if (c0 != nullptr) c0[row] = d[h][nt][0];
+          if (c1 != nullptr) c1[row] = d[h][nt][1];
         }
       }
     }
