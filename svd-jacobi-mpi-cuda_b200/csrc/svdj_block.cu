@@ -244,21 +244,25 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
   double(*W)[kD + 2] = Wb[cur];  // the live copy
 
   if (total_rot > 0 || a.force_update) {
-    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  thread (r = tid>>3, c4 = (tid&7)*4) computes 4 entries
-    const int r = tid >> 3, c0 = (tid & 7) * 4;
-    double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-#pragma unroll 8
-    for (int k2 = 0; k2 < kD; ++k2) {
-      const double wr = W[k2][r];
-      t0 = fma(wr, W[k2][c0 + 0], t0);
-      t1 = fma(wr, W[k2][c0 + 1], t1);
-      t2 = fma(wr, W[k2][c0 + 2], t2);
-      t3 = fma(wr, W[k2][c0 + 3], t3);
+    // Newton-Schulz: W <- W (1.5 I - 0.5 W^T W).  Both 32 x 32 x 32 products run as DMMA tiles: warp w owns the
+    // 8 x 16 piece (tile row w >> 1, tile columns 2 (w & 1), +1) of the result (as scalar FMAs they were bound
+    // by shared-memory loads, 5 per 4 FMAs).
+    const int g = lane >> 2, tg = lane & 3;
+    const int ti = (tid >> 5) >> 1, tj = 2 * ((tid >> 5) & 1);
+    {
+      double d0a = 0.0, d0b = 0.0, d1a = 0.0, d1b = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < kD / 4; ++ks) {
+        const double af = W[4 * ks + tg][8 * ti + g];
+        dmma884(d0a, d0b, af, W[4 * ks + tg][8 * tj + g]);
+        dmma884(d1a, d1b, af, W[4 * ks + tg][8 * tj + 8 + g]);
+      }
+      const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
+      T[r][c] = (r == c ? 1.5 : 0.0) - 0.5 * d0a;
+      T[r][c + 1] = (r == c + 1 ? 1.5 : 0.0) - 0.5 * d0b;
+      T[r][c + 8] = (r == c + 8 ? 1.5 : 0.0) - 0.5 * d1a;
+      T[r][c + 9] = (r == c + 9 ? 1.5 : 0.0) - 0.5 * d1b;
     }
-    T[r][c0 + 0] = (r == c0 + 0 ? 1.5 : 0.0) - 0.5 * t0;
-    T[r][c0 + 1] = (r == c0 + 1 ? 1.5 : 0.0) - 0.5 * t1;
-    T[r][c0 + 2] = (r == c0 + 2 ? 1.5 : 0.0) - 0.5 * t2;
-    T[r][c0 + 3] = (r == c0 + 3 ? 1.5 : 0.0) - 0.5 * t3;
     // Output slot of W's column i: the slots that hold real columns, in order, receive the eigenvalues in
     // descending order (stable).  Slots past the last column of a ragged block keep their (zero) column.
     if (tid < kD) {
@@ -277,20 +281,19 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
       rank_of[tid] = out;
     }
     __syncthreads();
-    double u0 = 0, u1 = 0, u2 = 0, u3 = 0;
-#pragma unroll 8
-    for (int k2 = 0; k2 < kD; ++k2) {
-      const double wr = W[r][k2];
-      u0 = fma(wr, T[k2][c0 + 0], u0);
-      u1 = fma(wr, T[k2][c0 + 1], u1);
-      u2 = fma(wr, T[k2][c0 + 2], u2);
-      u3 = fma(wr, T[k2][c0 + 3], u3);
+    double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < kD / 4; ++ks) {
+      const double af = W[8 * ti + g][4 * ks + tg];
+      dmma884(u0a, u0b, af, T[4 * ks + tg][8 * tj + g]);
+      dmma884(u1a, u1b, af, T[4 * ks + tg][8 * tj + 8 + g]);
     }
     double *wdst = wbuf + (size_t)pair * kD * kD;  // column-major: wdst[c*32 + r]
-    wdst[rank_of[c0 + 0] * kD + r] = u0;
-    wdst[rank_of[c0 + 1] * kD + r] = u1;
-    wdst[rank_of[c0 + 2] * kD + r] = u2;
-    wdst[rank_of[c0 + 3] * kD + r] = u3;
+    const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
+    wdst[rank_of[c] * kD + r] = u0a;
+    wdst[rank_of[c + 1] * kD + r] = u0b;
+    wdst[rank_of[c + 8] * kD + r] = u1a;
+    wdst[rank_of[c + 9] * kD + r] = u1b;
   }
   if (tid == 0) {
     wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;  // force_update: W = I still moves the columns
@@ -400,7 +403,7 @@ static constexpr int kUpdStages = 3;
 static constexpr int kUpdCtasPerSm = 4;
 static constexpr int kMaxCompactPairs = 2048;
 
-template <int STAGES>
+template <int STAGES>  // STAGES <= 3 (coltab sets)
 __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(const BlockArgs a, const unsigned k,
                                                                   const double *__restrict__ wbuf,
                                                                   const int *__restrict__ wflag,
@@ -409,6 +412,7 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
   extern __shared__ __align__(16) double tiles[];  // STAGES x 32 columns x kTileStride
   __shared__ unsigned short active[kMaxCompactPairs];
   __shared__ unsigned n_active_s;
+  __shared__ double *coltab[3][4][kD];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned g = lane >> 2, tg = lane & 3;
 
@@ -436,24 +440,42 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
   const unsigned t1 = (unsigned)(total * (blockIdx.x + 1) / gridDim.x);
   if (t0 >= t1) return;
 
-  auto issue_tile = [&](unsigned tau, int stage) {
-    const unsigned ap = tau / tpp, t = tau - ap * tpp;
+  // Column pointers of a block pair, worked out once per pair instead of once per tile and column (schedule,
+  // ragged-block and split/peer selection are dozens of integer instructions each).  Three sets: the loads run
+  // up to STAGES - 1 = 2 tiles ahead of the arithmetic, which for short pairs can be two pairs ahead.
+  auto fill_table = [&](unsigned ap) {
     const Pair bp = block_pair(a, k, active[ap]);
+    const unsigned set = ap % 3u;
+    for (unsigned i = threadIdx.x; i < 4 * kD; i += 128) {
+      const unsigned which = i >> 5, slot = i & 31u;  // 0: A load, 1: V load, 2: A store, 3: V store
+      const unsigned col = slot_col(bp.p, bp.q, slot, a.n);
+      double *ptr = nullptr;
+      if (col != kNoCol) ptr = (which < 2) ? col_ptr(a, which == 0, col) : col_ptr_store(a, which == 2, col);
+      coltab[set][which][slot] = ptr;
+    }
+  };
+
+  unsigned issue_ap = 0xffffffffu, issue_next = 0;
+  auto issue_tile = [&](unsigned tau, int stage) {
+    if (tau >= issue_next || issue_ap == 0xffffffffu) {  // CTA-uniform
+      issue_ap = tau / tpp;
+      issue_next = (issue_ap + 1) * tpp;
+      fill_table(issue_ap);
+      __syncthreads();
+    }
+    const unsigned t = tau - issue_ap * tpp;
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row = (isa ? t : t - tpa) * kTileRows + 2 * lane;
     double *dst = tiles + stage * kTileDoubles + 2 * lane;
+    double *const *tab = coltab[issue_ap % 3u][isa ? 0 : 1];
+    const int rb = (row < limit) ? ((row + 1 < limit) ? 16 : 8) : 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const unsigned slot = warp + 4 * i;
-      const unsigned col = slot_col(bp.p, bp.q, slot, a.n);
-      int bytes = 0;
-      const double *src = a.A;
-      if (col != kNoCol && row < limit) {
-        bytes = (row + 1 < limit) ? 16 : 8;
-        src = col_ptr(a, isa, col) + row;
-      }
-      cp_async16(dst + slot * kTileStride, src, bytes);
+      const double *base = tab[slot];
+      const bool ok = base != nullptr && rb != 0;
+      cp_async16(dst + slot * kTileStride, ok ? base + row : a.A, ok ? rb : 0);
     }
   };
 
@@ -468,8 +490,7 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
   }
 
   double wf[8][4];
-  Pair cur_bp = {0u, 0u};
-  unsigned cur_pair = 0xffffffffu;
+  unsigned cur_ap = 0xffffffffu, cur_next = 0;
   for (unsigned tau = t0; tau < t1; ++tau) {
     cp_async_wait<STAGES - 2>();
     __syncthreads();  // tile tau has landed for everyone; everyone is done with the stage refilled next
@@ -479,22 +500,21 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
     }
     cp_async_commit();
 
-    const unsigned ap = tau / tpp, t = tau - ap * tpp;
-    const unsigned pr = active[ap];
-    if (pr != cur_pair) {  // new block pair: its W (B fragments) and the columns this lane stores to
-      cur_pair = pr;
-      const Pair bp = block_pair(a, k, pr);
-      const double *w = wbuf + (size_t)pr * kD * kD;
+    if (tau >= cur_next || cur_ap == 0xffffffffu) {  // new block pair: its W as B fragments
+      cur_ap = tau / tpp;
+      cur_next = (cur_ap + 1) * tpp;
+      const double *w = wbuf + (size_t)active[cur_ap] * kD * kD;
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks)
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) wf[ks][nt] = w[(8 * nt + g) * kD + 4 * ks + tg];
-      cur_bp = bp;
     }
+    const unsigned t = tau - cur_ap * tpp;
     const bool isa = t < tpa;
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row0 = (isa ? t : t - tpa) * kTileRows + 16 * warp;
     const double *tile = tiles + ((tau - t0) % STAGES) * kTileDoubles + 16 * warp + g;
+    double *const *stab = coltab[cur_ap % 3u][isa ? 2 : 3] + 2 * tg;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       double af[8];
@@ -511,10 +531,9 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
       if (row < limit) {
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-          const unsigned c0 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg, a.n);
-          const unsigned c1 = slot_col(cur_bp.p, cur_bp.q, 8 * nt + 2 * tg + 1, a.n);
-          if (c0 != kNoCol) col_ptr_store(a, isa, c0)[row] = d[nt][0];
-          if (c1 != kNoCol) col_ptr_store(a, isa, c1)[row] = d[nt][1];
+          double *const c0 = stab[8 * nt], *const c1 = stab[8 * nt + 1];
+          if (c0 != nullptr) c0[row] = d[nt][0];
+          if (c1 != nullptr) c1[row] = d[nt][1];
         }
       }
     }
