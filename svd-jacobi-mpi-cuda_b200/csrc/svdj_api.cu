@@ -229,7 +229,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (int rc = d_counters.alloc(sizeof(SweepCounters) * (size_t)o.max_sweeps)) return rc;
   if (int rc = h_counters.alloc(sizeof(SweepCounters))) return rc;
   SVDJ_CUDA_TRY(cudaMemsetAsync(d_counters.p, 0, sizeof(SweepCounters) * (size_t)o.max_sweeps, stream));
-  DevBuf d_gpart, d_w, d_wflag;
+  DevBuf d_gpart, d_w, d_wflag, d_gcache;
   if (block) {
     // sized for either block width (the 32-wide kernels need more of everything per pair, for half the pairs)
     size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
@@ -241,6 +241,8 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     if (int rc = d_gpart.alloc(sizeof(double) * gp)) return rc;
     if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
     if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
+    // per column block of 32: its Gram matrix as the last eigen-solve left it (8 KiB per block)
+    if (int rc = d_gcache.alloc(sizeof(double) * 1024 * (size_t)((n + 31) / 32 + 1))) return rc;
   } else if (l1_uses_split(m, n)) {
     if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
   }
@@ -253,11 +255,11 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   // block width: 16 by default; 32 on request (opts.block == 32 or SVDJ_BLOCK=32) when the layout allows it
   bool wide = false;
   if (block) {
-    // 0 = choose: measured on B200 (profiles/r1_block_widths.md) the 64-column block pairs win from n = 4096 up
+    // 0 = choose: measured on B200 (profiles/r1_block_widths.md) the 64-column block pairs win from n = 2048 up
     // (half the steps and half the HBM traffic per sweep, fewer sweeps), the 32-column ones below
     int want = o.block;
     if (const char *env = std::getenv("SVDJ_BLOCK")) want = std::atoi(env);
-    if (want == 0) want = (n >= 4096) ? 32 : 16;
+    if (want == 0) want = (n >= 2048) ? 32 : 16;
     if (want == 32 && blk32_num_blocks(n) >= 2) {
       BlockArgs probe_args;
       probe_args.A = dA;
@@ -292,8 +294,12 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   b.sched = 0;
   b.sort_cols = 1;
   b.vranks = 1;
+  b.gcache = wide ? d_gcache.as<double>() : nullptr;  // the 64-column kernels drop it where it does not apply
+  if (const char *env = std::getenv("SVDJ_GCACHE")) {
+    if (env[0] == '0') b.gcache = nullptr;
+  }
   // two-level tournament ordering (the ring's ordering with virtual ranks) when the blocks divide evenly
-  if (block && n % (wide ? 32 : 16) == 0) {
+  if (block) {
     // P = 4 virtual ranks where the blocks divide evenly (measured best of 1, 2, 4, 16 at 1024..4096), else 2,
     // else the flat ordering; SVDJ_VRANKS overrides (0 = flat)
     int P = (nb % 8u == 0) ? 4 : (nb % 4u == 0) ? 2 : 0;

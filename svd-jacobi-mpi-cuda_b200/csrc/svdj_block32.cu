@@ -53,6 +53,10 @@ __device__ __forceinline__ void gram32_ksteps(const double *__restrict__ tile, d
   }
 }
 
+// CROSS: only the 16 tiles of X_p^T X_q (the cross block of the Gram matrix); the two diagonal blocks then come
+// from the per-block cache the eigen-solve maintains (BlockArgs::gcache).  Every warp accumulates all 16 tiles over
+// a quarter of the tile's rows.  Output layout: tile (ti, tj) at gpart[(4 ti + tj) * 64 ...], same fragment order.
+template <bool CROSS>
 __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, const unsigned k,
                                                          const unsigned rows_per_split,
                                                          double *__restrict__ gpart) {
@@ -64,20 +68,20 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
   const unsigned r1 = min(a.m, r0 + rows_per_split);
   const unsigned ntiles = r0 < r1 ? (r1 - r0 + kG32Rows - 1) / kG32Rows : 0;
 
+  const double *cptr[16];  // this thread copies column slots warp + 4 i (nullptr: past the last column)
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const unsigned c = slot_col32(bp.p, bp.q, warp + 4 * i, a.n);
+    cptr[i] = (c != kNoCol) ? col_ptr(a, true, c) : nullptr;
+  }
   auto issue_tile = [&](unsigned t, int stage) {
     const unsigned row = r0 + t * kG32Rows + 2 * lane;
     double *dst = tiles + stage * kG32TileDoubles + 2 * lane;
-#pragma unroll 4
+    const int rb = (row < r1) ? ((row + 1 < r1) ? 16 : 8) : 0;
+#pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const unsigned slot = warp + 4 * i;
-      const unsigned c = slot_col32(bp.p, bp.q, slot, a.n);
-      int bytes = 0;
-      const double *src = a.A;
-      if (c != kNoCol && row < r1) {
-        bytes = (row + 1 < r1) ? 16 : 8;
-        src = col_ptr(a, true, c) + row;
-      }
-      cp_async16(dst + slot * kG32Stride, src, bytes);
+      const bool ok = cptr[i] != nullptr && rb != 0;
+      cp_async16(dst + (warp + 4 * i) * kG32Stride, ok ? cptr[i] + row : a.A, ok ? rb : 0);
     }
   };
 
@@ -90,9 +94,10 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
     }
     cp_async_commit();
   }
-  double acc[18][2];
+  constexpr int kAcc = CROSS ? 16 : 18;
+  double acc[kAcc][2];
 #pragma unroll
-  for (int t = 0; t < 18; ++t) acc[t][0] = acc[t][1] = 0.0;
+  for (int t = 0; t < kAcc; ++t) acc[t][0] = acc[t][1] = 0.0;
   const unsigned gsel = warp & 1, rh = warp >> 1;
 
   for (unsigned t = 0; t < ntiles; ++t) {
@@ -103,24 +108,43 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
       ++issued;
     }
     cp_async_commit();
-    const double *tile = tiles + (t % kG32Stages) * kG32TileDoubles + g * kG32Stride + 32 * rh + tg;
-    if (gsel == 0) gram32_ksteps<0>(tile, acc);
-    else gram32_ksteps<1>(tile, acc);
+    if constexpr (CROSS) {
+      const double *tile = tiles + (t % kG32Stages) * kG32TileDoubles + g * kG32Stride + 16 * warp + tg;
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        double f[kTG];
+#pragma unroll
+        for (int gi = 0; gi < kTG; ++gi) f[gi] = tile[(8 * gi) * kG32Stride + 4 * ks];
+#pragma unroll
+        for (int ti = 0; ti < 4; ++ti)
+#pragma unroll
+          for (int tj = 0; tj < 4; ++tj) dmma884(acc[4 * ti + tj][0], acc[4 * ti + tj][1], f[ti], f[4 + tj]);
+      }
+    } else {
+      const double *tile = tiles + (t % kG32Stages) * kG32TileDoubles + g * kG32Stride + 32 * rh + tg;
+      if (gsel == 0) gram32_ksteps<0>(tile, acc);
+      else gram32_ksteps<1>(tile, acc);
+    }
   }
   cp_async_wait<0>();
-  __syncthreads();  // the tile buffers become the reduction buffer: [4 warps][18 tiles][64]
+  __syncthreads();  // the tile buffers become the reduction buffer: [4 warps][kAcc tiles][64]
   double *red = tiles;
 #pragma unroll
-  for (int t = 0; t < 18; ++t) {
-    red[(warp * 18 + t) * 64 + lane * 2 + 0] = acc[t][0];
-    red[(warp * 18 + t) * 64 + lane * 2 + 1] = acc[t][1];
+  for (int t = 0; t < kAcc; ++t) {
+    red[(warp * kAcc + t) * 64 + lane * 2 + 0] = acc[t][0];
+    red[(warp * kAcc + t) * 64 + lane * 2 + 1] = acc[t][1];
   }
   __syncthreads();
   double *dst = gpart + ((size_t)blockIdx.x * gridDim.y + blockIdx.y) * kGramPart32;
-  for (unsigned i = threadIdx.x; i < kGramPart32; i += 128) {
-    const unsigned t = i >> 6, e = i & 63;
-    const unsigned gs = t & 1, lt = t >> 1;  // tile t lives in warps gs and gs + 2 as local tile lt
-    dst[i] = red[((gs)*18 + lt) * 64 + e] + red[((gs + 2) * 18 + lt) * 64 + e];
+  if constexpr (CROSS) {
+    for (unsigned i = threadIdx.x; i < 16 * 64; i += 128)
+      dst[i] = (red[i] + red[16 * 64 + i]) + (red[2 * 16 * 64 + i] + red[3 * 16 * 64 + i]);
+  } else {
+    for (unsigned i = threadIdx.x; i < kGramPart32; i += 128) {
+      const unsigned t = i >> 6, e = i & 63;
+      const unsigned gs = t & 1, lt = t >> 1;  // tile t lives in warps gs and gs + 2 as local tile lt
+      dst[i] = red[((gs)*18 + lt) * 64 + e] + red[((gs + 2) * 18 + lt) * 64 + e];
+    }
   }
 }
 
@@ -165,19 +189,41 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   const unsigned pair = blockIdx.x;
 
   const double *src = gpart + (size_t)pair * splits * kGramPart32;
-  for (unsigned i = tid; i < kGramPart32; i += 1024) {
-    double s = 0.0;
-    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
-    const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
-    int ti = 0, rem = t;  // t -> (ti, tj): rows of 8, 7, ..., 1 tiles
-    while (rem >= kTG - ti) {
-      rem -= kTG - ti;
-      ++ti;
+  const bool cached = a.gcache != nullptr && a.cross_only != 0;
+  if (cached) {
+    // cross block from this step's partial sums (16 tiles), the two diagonal blocks from the cache: they are the
+    // rotated Gram blocks the eigen-solves of the blocks' previous pairs left behind (refreshed from the columns
+    // themselves in the first step of every sweep, which is also the only step that tests intra-block pairs)
+    const Pair bp = block_pair(a, k, pair);
+    for (unsigned i = tid; i < 16 * 64; i += 1024) {
+      double s = 0.0;
+      for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+      const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
+      const int r = 8 * (t >> 2) + (l >> 2), c = 32 + 8 * (t & 3) + 2 * (l & 3) + e;
+      G0[r][c] = s;
+      G0[c][r] = s;
     }
-    const int tj = ti + rem;
-    const int r = 8 * ti + (l >> 2), c = 8 * tj + 2 * (l & 3) + e;
-    G0[r][c] = s;
-    if (ti != tj) G0[c][r] = s;
+    const double *cp = a.gcache + (size_t)bp.p * (kB32 * kB32), *cq = a.gcache + (size_t)bp.q * (kB32 * kB32);
+    {
+      const int r = tid >> 5, c = tid & 31;
+      G0[r][c] = cp[tid];
+      G0[32 + r][32 + c] = cq[tid];
+    }
+  } else {
+    for (unsigned i = tid; i < kGramPart32; i += 1024) {
+      double s = 0.0;
+      for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+      const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
+      int ti = 0, rem = t;  // t -> (ti, tj): rows of 8, 7, ..., 1 tiles
+      while (rem >= kTG - ti) {
+        rem -= kTG - ti;
+        ++ti;
+      }
+      const int tj = ti + rem;
+      const int r = 8 * ti + (l >> 2), c = 8 * tj + 2 * (l & 3) + e;
+      G0[r][c] = s;
+      if (ti != tj) G0[c][r] = s;
+    }
   }
   for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
   if (tid == 0) fresh_max = 0ull;
@@ -337,6 +383,15 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       rank_of[tid] = out;
     }
     __syncthreads();
+    if (a.gcache != nullptr) {  // the rotated diagonal blocks, in the order the columns are written back in
+      const Pair bp = block_pair(a, k, pair);
+      for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
+        const int orow = rank_of[i >> 6], ocol = rank_of[i & 63];
+        if ((orow < 32) == (ocol < 32))
+          a.gcache[(size_t)(orow < 32 ? bp.p : bp.q) * (kB32 * kB32) + (orow & 31) * kB32 + (ocol & 31)] =
+              Gc[i >> 6][i & 63];
+      }
+    }
     double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
 #pragma unroll 4
     for (int ks = 0; ks < 16; ++ks) {
@@ -350,6 +405,13 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     wdst[rank_of[c + 1] * kD64 + r] = u0b;
     wdst[rank_of[c + 8] * kD64 + r] = u1a;
     wdst[rank_of[c + 9] * kD64 + r] = u1b;
+  }
+  else if (a.gcache != nullptr && !cross) {  // full step, nothing rotated: refresh the cache from the fresh matrix
+    const Pair bp = block_pair(a, k, pair);
+    const int r = tid >> 5, c = tid & 31;
+    double(*Gc)[kE32Stride] = cur ? G1 : G0;
+    a.gcache[(size_t)bp.p * (kB32 * kB32) + tid] = Gc[r][c];
+    a.gcache[(size_t)bp.q * (kB32 * kB32) + tid] = Gc[32 + r][32 + c];
   }
   if (tid == 0) {
     wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;
@@ -571,8 +633,11 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   // later steps: cross pairs only
   a.cross_only = (k > 1 && (a.nb % 2 == 0) && !blk_full_inner()) ? 1 : 0;  // both orderings (sched 0 and 2)
   static const cudaError_t attrs = [] {
-    cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(blk32_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(blk32_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kE32Smem);
     if (e == cudaSuccess)
@@ -588,7 +653,12 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   const unsigned splits = gram32_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + kG32Rows - 1) / kG32Rows * kG32Rows;
-  blk32_gram_kernel<<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
+  // The Gram cache needs whole blocks and every block in a pair of the sweep's first (full) step
+  if (a.gcache != nullptr && (a.n % kB32 != 0 || a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
+  if (a.gcache != nullptr && a.cross_only)
+    blk32_gram_kernel<true><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
+  else
+    blk32_gram_kernel<false><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
   blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
   if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   blk32_update_kernel<<<sm_count * kU32CtasPerSm, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
