@@ -646,12 +646,6 @@ static bool blk_force_plain_update() {
   return e != nullptr && e[0] == '1';
 }
 
-// flat ordering (sched 0): full eigen-solve in every step unless SVDJ_CROSS_FLAT=1 (it needs fewer sweeps that way)
-static bool blk_cross_flat() {
-  const char *e = std::getenv("SVDJ_CROSS_FLAT");
-  return e != nullptr && e[0] == '1';
-}
-
 unsigned blk_num_blocks(size_t n) { return (unsigned)((n + kBW - 1) / kBW); }
 
 static unsigned gram_splits(size_t m, unsigned pairs) {
@@ -702,7 +696,7 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
   {
     const char *e = std::getenv("SVDJ_FULL_INNER");
     const bool always_full = e != nullptr && e[0] == '1';
-    a.cross_only = (!always_full && (a.sched == 1 || (k > 1 && a.nb % 2 == 0 && (a.sched == 2 || blk_cross_flat())))) ? 1 : 0;
+    a.cross_only = (!always_full && (a.sched == 1 || (k > 1 && a.nb % 2 == 0))) ? 1 : 0;
   }
   const unsigned splits = gram_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   const unsigned pair = blockIdx.x;
 
   const double *src = gpart + (size_t)pair * splits * kGramPart32;
-  const bool cached = a.gcache != nullptr && a.cross_only != 0;
+  const bool cached = a.gcache != nullptr && a.gram_mode == 2;
   if (cached) {
     // cross block from this step's partial sums (16 tiles), the two diagonal blocks from the cache: they are the
     // rotated Gram blocks the eigen-solves of the blocks' previous pairs left behind (refreshed from the columns
@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     wdst[rank_of[c + 8] * kD64 + r] = u1a;
     wdst[rank_of[c + 9] * kD64 + r] = u1b;
   }
-  else if (a.gcache != nullptr && !cross) {  // full step, nothing rotated: refresh the cache from the fresh matrix
+  else if (a.gcache != nullptr && a.gram_mode == 1) {  // refresh step, nothing rotated: the fresh diagonal blocks
     const Pair bp = block_pair(a, k, pair);
     const int r = tid >> 5, c = tid & 31;
     double(*Gc)[kE32Stride] = cur ? G1 : G0;
@@ -507,12 +507,13 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     double *dst = tiles + stage * kU32TileDoubles + rin;
     double *const *tab = coltab[issue_ap & 1u][isa ? 0 : 1];
     const int rb = (row < limit) ? ((row + 1 < limit) ? 16 : 8) : 0;
+    const double *base[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) base[i] = tab[warp + 8 * i];  // all loads first: their latencies overlap
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const unsigned slot = warp + 8 * i;
-      const double *base = tab[slot];
-      const bool ok = base != nullptr && rb != 0;
-      cp_async16(dst + slot * kU32Stride, ok ? base + row : a.A, ok ? rb : 0);
+      const bool ok = base[i] != nullptr && rb != 0;
+      cp_async16(dst + (warp + 8 * i) * kU32Stride, ok ? base[i] + row : a.A, ok ? rb : 0);
     }
   };
 
@@ -568,15 +569,20 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
       dmma884(d[1][3][0], d[1][3][1], a1, b23.y);
     }
     double *const *stab = coltab[cur_ap & 1u][isa ? 2 : 3] + 32 * nhalf + 2 * tg;
+    double *cst[8];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
-      double *const c0 = stab[8 * nt], *const c1 = stab[8 * nt + 1];
+      cst[2 * nt] = stab[8 * nt];
+      cst[2 * nt + 1] = stab[8 * nt + 1];
+    }
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const unsigned row = row0 + 8 * h + g;
-        if (row < limit) {
-          if (c0 != nullptr) c0[row] = d[h][nt][0];
-          if (c1 != nullptr) c1[row] = d[h][nt][1];
+    for (int h = 0; h < 2; ++h) {
+      const unsigned row = row0 + 8 * h + g;
+      if (row < limit) {
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          if (cst[2 * nt] != nullptr) cst[2 * nt][row] = d[h][nt][0];
+          if (cst[2 * nt + 1] != nullptr) cst[2 * nt + 1][row] = d[h][nt][1];
         }
       }
     }
@@ -614,24 +620,41 @@ void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_do
 bool blk32_supported(const BlockArgs &a) {
   const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
                        (!a.rotate_v || ((a.ldv % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.V) & 15) == 0)));
-  return aligned && (a.nb / 2) <= (unsigned)kMaxPairs32 && a.nb >= 2 && a.A2 == nullptr;
+  const bool aligned2 = a.A2 == nullptr || (((reinterpret_cast<uintptr_t>(a.A2) & 15) == 0) &&
+                                           (!a.rotate_v || ((reinterpret_cast<uintptr_t>(a.V2) & 15) == 0)));
+  return aligned && aligned2 && (a.nb / 2) <= (unsigned)kMaxPairs32 && a.nb >= 2;
 }
 
 int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
                       unsigned long long *launches, const BlockProbe *probe) {
   const unsigned pairs = a_in.nb / 2;
   if (pairs == 0) return SVDJ_OK;
-  BlockArgs a = a_in;  // single buffer only
-  a.split = a.n;
-  a.A2 = a.A;
-  a.V2 = a.V;
-  a.A_st = a.A;
-  a.V_st = a.V;
-  a.A2_st = a.A;
-  a.V2_st = a.V;
-  // first step of a sweep: full eigen-solve (every block is in exactly one pair when their number is even);
-  // later steps: cross pairs only
-  a.cross_only = (k > 1 && (a.nb % 2 == 0) && !blk_full_inner()) ? 1 : 0;  // both orderings (sched 0 and 2)
+  BlockArgs a = a_in;
+  if (a.A2 == nullptr || a.split >= a.n) {  // single buffer
+    a.split = a.n;
+    a.A2 = a.A;
+    a.V2 = a.V;
+  } else {  // pre-bias the second buffers so that kernels index every column with its own number
+    a.A2 = a.A2 - (size_t)a.split * a.lda;
+    if (a.V2 != nullptr) a.V2 = a.V2 - (size_t)a.split * a.ldv;
+  }
+  // store targets: the load buffers unless the caller redirected them (already as plain block bases)
+  a.A_st = a_in.A_st ? a_in.A_st : a_in.A;
+  a.V_st = a_in.V_st ? a_in.V_st : a_in.V;
+  if (a_in.A2 == nullptr || a_in.split >= a_in.n) {
+    a.A2_st = a.A_st;
+    a.V2_st = a.V_st;
+  } else {
+    a.A2_st = (a_in.A2_st ? a_in.A2_st : a_in.A2) - (size_t)a.split * a.lda;
+    double *v2 = a_in.V2_st ? a_in.V2_st : a_in.V2;
+    a.V2_st = v2 ? v2 - (size_t)a.split * a.ldv : nullptr;
+  }
+  // first step of a sweep or ring phase: full eigen-solve (every block is in exactly one pair when their number is
+  // even); later steps, and every step of the ring's bipartite CROSS phase: cross pairs only
+  a.cross_only = (!blk_full_inner() && (a.sched == 1 || (k > 1 && a.nb % 2 == 0))) ? 1 : 0;
+  // The Gram cache needs whole blocks and every block in a pair of the first step, which refreshes it
+  if (a.gcache != nullptr && (a.n % kB32 != 0 || a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
+  a.gram_mode = (a.gcache == nullptr) ? 0 : (k == 1 ? 1 : 2);
   static const cudaError_t attrs = [] {
     cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
@@ -653,9 +676,7 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   const unsigned splits = gram32_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + kG32Rows - 1) / kG32Rows * kG32Rows;
-  // The Gram cache needs whole blocks and every block in a pair of the sweep's first (full) step
-  if (a.gcache != nullptr && (a.n % kB32 != 0 || a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
-  if (a.gcache != nullptr && a.cross_only)
+  if (a.gram_mode == 2)
     blk32_gram_kernel<true><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
   else
     blk32_gram_kernel<false><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);

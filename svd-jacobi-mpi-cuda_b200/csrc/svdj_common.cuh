@@ -194,6 +194,7 @@ struct BlockArgs {
   int force_update = 0;
   int vranks = 1;      // sched 2: number of virtual ranks P of the two-level tournament
   double *gcache = nullptr;  // b = 32: per column block, its 32 x 32 Gram matrix as the last eigen-solve left it
+  int gram_mode = 0;   // b = 32 with gcache: 1 = full Gram, refresh the cache; 2 = cross block only, diagonal blocks from the cache
   int cross_only = 0;  // eigen-solve visits only the pairs with one column in each block (set per step by the launchers)
   double tol;
   int threshold_mode;

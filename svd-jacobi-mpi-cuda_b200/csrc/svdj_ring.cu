@@ -9,6 +9,7 @@
 // the update kernel).  This file is the per-rank compute: a "phase" = all round-robin steps over the
 // blocks of the two buffers (SVDJ_PHASE_ALL: every pair of local columns; SVDJ_PHASE_CROSS: only pairs
 // with one column in each buffer).
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -22,6 +23,7 @@ struct RingWorkspace {
   double *wbuf = nullptr;
   int *wflag = nullptr;
   double *norms = nullptr;
+  double *gcache = nullptr;  // 64-column kernels: Gram matrix of every local column block of 32
 };
 
 static void ws_free(RingWorkspace *w) {
@@ -30,6 +32,7 @@ static void ws_free(RingWorkspace *w) {
   if (w->wbuf) cudaFree(w->wbuf);
   if (w->wflag) cudaFree(w->wflag);
   if (w->norms) cudaFree(w->norms);
+  if (w->gcache) cudaFree(w->gcache);
   delete w;
 }
 
@@ -48,9 +51,14 @@ int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out) {
   if (!w) return SVDJ_ERR_ALLOC;
   w->m = m;
   w->ncols = ncols_local;
-  size_t gp = 0, wd = 0, fl = 0;
+  size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
   blk_scratch_sizes(m, ncols_local, &gp, &wd, &fl);
+  blk32_scratch_sizes(m, ncols_local, &gp2, &wd2, &fl2);  // either block width
+  gp = gp > gp2 ? gp : gp2;
+  wd = wd > wd2 ? wd : wd2;
+  fl = fl > fl2 ? fl : fl2;
   cudaError_t e = cudaMalloc(&w->gpart, sizeof(double) * gp);
+  if (e == cudaSuccess) e = cudaMalloc(&w->gcache, sizeof(double) * 1024 * (ncols_local / 32 + 1));
   if (e == cudaSuccess) e = cudaMalloc(&w->wbuf, sizeof(double) * wd);
   if (e == cudaSuccess) e = cudaMalloc(&w->wflag, sizeof(int) * fl);
   if (e == cudaSuccess) e = cudaMalloc(&w->norms, sizeof(double) * ncols_local);
@@ -91,7 +99,10 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
   b.n = (unsigned)(2 * w);
   b.vrows = (unsigned)vrows;
   b.rotate_v = rotate_v ? 1 : 0;
-  b.nb = blk_num_blocks(2 * w);
+  // 64-column block pairs where the local blocks divide into column blocks of 32 (SVDJ_BLOCK=16 forces the narrow ones)
+  bool wide = (w % 32 == 0);
+  if (const char *env = std::getenv("SVDJ_BLOCK")) wide = wide && std::atoi(env) != 16;
+  b.nb = wide ? blk32_num_blocks(2 * w) : blk_num_blocks(2 * w);
   b.A2 = dA_right;
   b.V2 = dV_right;
   b.split = (unsigned)w;
@@ -101,6 +112,15 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
   b.threshold_mode = SVDJ_THRESH_REL;
   b.max_inner_sweeps = inner_sweeps > 0 ? inner_sweeps : 2;
   b.counters = reinterpret_cast<SweepCounters *>(d_counters);
+  if (wide) {
+    wide = blk32_supported(b);
+    if (!wide) b.nb = blk_num_blocks(2 * w);
+  }
+  // the cache is refreshed in the first step of every phase (the blocks may just have arrived from a neighbour)
+  b.gcache = wide ? W->gcache : nullptr;
+  if (const char *env = std::getenv("SVDJ_GCACHE")) {
+    if (env[0] == '0') b.gcache = nullptr;
+  }
   const unsigned steps = (phase == SVDJ_PHASE_CROSS) ? b.nb / 2 : (unsigned)svdj_num_steps(b.nb);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   for (unsigned k = 1; k <= steps; ++k) {
@@ -113,7 +133,7 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
       b.V2_st = dstV_right ? dstV_right : dV_right;
       b.force_update = 1;
     }
-    if (int rc = blk_launch_step(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr)) return rc;
+    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr)) return rc;
   }
   return SVDJ_OK;
 }
