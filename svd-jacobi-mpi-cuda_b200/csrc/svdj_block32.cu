@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   __shared__ unsigned long long fresh_max;
   __shared__ int rank_of[kD64];
   __shared__ int valid[kD64];
-  __shared__ double rot_c[32], rot_s[32];
+  __shared__ double rot_c[32], rot_s[32], rin_al[32], rin_be[32], rin_ga[32];
   __shared__ int sweep_rot_s;
   const unsigned tid = threadIdx.x, lane = tid & 31;
   const unsigned pair = blockIdx.x;
@@ -277,8 +277,82 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       any |= (al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2) ? 1 : 0;
     }
   }
+  if (cross && tid < 32) {  // rotation inputs of the first CROSS step
+    rin_al[tid] = G0[tid][32 + tid];
+    rin_be[tid] = G0[tid][tid];
+    rin_ga[tid] = G0[32 + tid][32 + tid];
+  }
   any = __syncthreads_or(any);
-  for (int sw = 0; sw < (any ? a.max_inner_sweeps : 0); ++sw) {
+  if (cross && any) {
+    // CROSS schedule with the matrices in registers.  In this schedule the top slots stay and the bottom slots move
+    // down by one per step, so of a thread's 2 x 2 block g11 stays where it is, g12 comes from the next lane
+    // (shuffle), and only the bottom row (g21, g22) changes warps and goes through shared memory; W's rows never
+    // move, so W lives in registers for the whole solve.  (With G and W round-tripping through shared memory the
+    // loop was bound by shared-memory bandwidth: 16 accesses per thread and step, now 4.)  The inputs of the
+    // next step's rotations are posted by the threads that produce them.
+    double g11 = G0[w1][l2], g12 = G0[w1][32 + l2], g21 = G0[32 + w1][l2], g22 = G0[32 + w1][32 + l2];
+    double wp0 = (w1 == l2) ? 1.0 : 0.0, wq0 = 0.0, wp1 = 0.0, wq1 = (w1 == l2) ? 1.0 : 0.0;
+    double(*X)[kE32Stride] = G1;  // rows 0..31: g21 of thread (row, lane); rows 32..63: g22
+    const int up = (l2 + 1) & 31, wdst = (w1 + 31) & 31, ldst = (l2 + 31) & 31;
+    for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+      int sweep_rot = 0;  // counted by warp 0
+      for (int t = 0; t < 32; ++t) {
+        if (w1 == 0) {
+          const double al = rin_al[l2], be = rin_be[l2], ga = rin_ga[l2];
+          const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
+          double c = 1.0, sn = 0.0;
+          if (rot) fast_rotation(al, be, ga, c, sn);
+          rot_c[l2] = c;
+          rot_s[l2] = sn;
+          sweep_rot += __popc(__ballot_sync(0xffffffffu, rot));
+        }
+        __syncthreads();
+        const double c2 = rot_c[l2], s2 = rot_s[l2], c1 = rot_c[w1], s1 = rot_s[w1];
+        const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
+        const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
+        const double n11 = c1 * h11 - s1 * h21;
+        double n21 = s1 * h11 + c1 * h21;
+        double n12 = c1 * h12 - s1 * h22;
+        const double n22 = s1 * h12 + c1 * h22;
+        if (w1 == l2) {
+          if (s1 != 0.0) {
+            n12 = 0.0;  // the rotated pair is orthogonal by construction
+            n21 = 0.0;
+          }
+          rin_be[w1] = n11;    // G[j][j] of the next step, j = w1
+          rin_ga[wdst] = n22;  // G[32+j][32+j] of the next step, j = w1 - 1
+        }
+        if (l2 == ((w1 + 1) & 31)) rin_al[w1] = n12;  // G[j][32+j] of the next step, j = w1
+        X[wdst][l2] = n21;
+        X[32 + wdst][ldst] = n22;
+        g11 = n11;
+        g12 = __shfl_sync(0xffffffffu, n12, up);
+        const double nq0 = s2 * wp0 + c2 * wq0, nq1 = s2 * wp1 + c2 * wq1;
+        wp0 = c2 * wp0 - s2 * wq0;
+        wp1 = c2 * wp1 - s2 * wq1;
+        wq0 = __shfl_sync(0xffffffffu, nq0, up);
+        wq1 = __shfl_sync(0xffffffffu, nq1, up);
+        __syncthreads();
+        g21 = X[w1][l2];
+        g22 = X[32 + w1][l2];
+      }
+      if (tid == 0) sweep_rot_s = sweep_rot;
+      __syncthreads();
+      const int sr = sweep_rot_s;
+      total_rot += sr;
+      if (sr == 0) break;
+    }
+    G0[w1][l2] = g11;
+    G0[w1][32 + l2] = g12;
+    G0[32 + w1][l2] = g21;
+    G0[32 + w1][32 + l2] = g22;
+    W[w1][l2] = wp0;
+    W[w1][32 + l2] = wq0;
+    W[w1 + 32][l2] = wp1;
+    W[w1 + 32][32 + l2] = wq1;
+    __syncthreads();
+  }
+  for (int sw = 0; sw < ((any && !cross) ? a.max_inner_sweeps : 0); ++sw) {
     int sweep_rot = 0;  // counted by warp 0
     for (int t = 0; t < nsteps; ++t) {
       double(*Gc)[kE32Stride] = cur ? G1 : G0;
@@ -600,13 +674,22 @@ static bool blk_full_inner() {  // SVDJ_FULL_INNER=1: always the full schedule (
 
 unsigned blk32_num_blocks(size_t n) { return (unsigned)((n + kB32 - 1) / kB32); }
 
+// Row splits of the Gram kernel: as many as fit in ONE wave of resident CTAs (2 per SM), rounded so that every
+// split is a whole number of 64-row tiles.  (Two waves, the first version, left the second wave 16 % full at
+// 4096 x 4096 and gave the eigen-solve 10 partial sums to add instead of 4.)  SVDJ_GRAM_WAVES overrides.
 static unsigned gram32_splits(size_t m, unsigned pairs) {
-  size_t want = (2 * 2 * 148 + pairs - 1) / (pairs ? pairs : 1);  // 2 CTAs per SM, two waves
-  size_t cap = (m + kG32Rows - 1) / kG32Rows;
-  if (want > cap) want = cap;
+  static const int waves = [] {
+    const char *e = std::getenv("SVDJ_GRAM_WAVES");
+    const int w = e ? std::atoi(e) : 1;
+    return w >= 1 ? w : 1;
+  }();
+  const size_t tiles = (m + kG32Rows - 1) / kG32Rows;
+  size_t want = ((size_t)waves * 2 * 148) / (pairs ? pairs : 1);
   if (want < 1) want = 1;
+  if (want > tiles) want = tiles;
   if (want > 1024) want = 1024;
-  return (unsigned)want;
+  const size_t tiles_per_split = (tiles + want - 1) / want;
+  return (unsigned)((tiles + tiles_per_split - 1) / tiles_per_split);
 }
 
 void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
@@ -676,14 +759,23 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   const unsigned splits = gram32_splits(a.m, pairs);
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + kG32Rows - 1) / kG32Rows * kG32Rows;
+  // SVDJ_PROBE_KERNEL=1|2 moves the probe events from the update kernel to K1 or K2 (profiling aid)
+  static const int probe_kernel = [] {
+    const char *e = std::getenv("SVDJ_PROBE_KERNEL");
+    return e ? std::atoi(e) : 3;
+  }();
+  if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   if (a.gram_mode == 2)
     blk32_gram_kernel<true><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
   else
     blk32_gram_kernel<false><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
+  if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
-  if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
+  if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   blk32_update_kernel<<<sm_count * kU32CtasPerSm, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
-  if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());
   return SVDJ_OK;

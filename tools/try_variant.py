@@ -19,5 +19,5 @@ for sz in a.sizes.split(","):
     ref = torch.linalg.svdvals(dA0.T)
     eye = torch.eye(n, dtype=torch.float64, device="cuda")
     print(f"{m}x{n} variant={st.variant} rc={st.rc} sweeps={st.sweeps} conv={st.converged} applied={st.applied} t_sweeps={st.seconds_sweeps*1e3:.1f} ms fin={st.seconds_finalize*1e3:.1f} ms total={st.seconds_total*1e3:.1f} ms "
-          f"launches={st.launches} sig={float((S-ref).abs().max()/ref[0]):.2e} orthU={float((U.T@U-eye).abs().max()):.2e} "
+          f"launches={st.launches} probe_us={st.step_kernel_ms*1e3:.1f} sig={float((S-ref).abs().max()/ref[0]):.2e} orthU={float((U.T@U-eye).abs().max()):.2e} "
           f"orthV={float((V.T@V-eye).abs().max()):.2e} resid={float(torch.linalg.norm(dA0.T-(U*S)@V.T)/torch.linalg.norm(dA0)):.2e} off={st.last_offdiag:.2e}")
