@@ -383,11 +383,13 @@ def run_svdj(args):
         if width == 32:
             # 0.31 * 32 = 10 flop/B against a ridge of 36.9 TF / 6.45 TB/s = 5.7: the FP64 tensor pipe bounds it
             roofline = {"bound": "tensor", "achieved": tfs, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tfs / dmma_peak,
-                        "traffic": 486.6e6 if full else None,
+                        # ncu --set full, one launch with every pair active: dram read 272.0 MB + write 212.5 MB
+                        # (profiles/r1_final.md); the algorithmic figure of such a launch is 268 + 268 MB
+                        "traffic": 484.5e6 if full else None,
                         "peak_source": "measured DMMA (mma.sync.m8n8k4.f64) issue peak on this pool, tools/fp64_peak.cu; "
                                        "MEASURED_PEAKS.json has no FP64 figure (cuBLAS DGEMM here: 35.5)",
                         "kernel": "blk32_update_kernel (X<-XW, Y<-YW for 64-column block pairs; FP64 DMMA tiles, "
-                                  "W in shared memory, cp.async staged)",
+                                  "W in shared memory in fragment order, cp.async staged, per-pair column pointer tables)",
                         "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
                         "launches_probed": int(launches),
                         "hbm": {"alg_bytes_per_launch": bytes_per_launch, "achieved_gbs": gbs, "peak_gbs": peak,

@@ -209,6 +209,14 @@ size_t svdj_num_steps(size_t n);
  * into pq[0..2*(n/2)) and returns their count (main.cu:526-545, 971-990). */
 size_t svdj_schedule_step(size_t n, size_t step, size_t *pq);
 
+/* Host-side copy of the schedule the block path uses over its nb column blocks: the nb/2 block pairs (p < q for
+ * the two-level ordering), 0-based, of `step` (0-based, < svdj_num_steps(nb)).  vranks <= 1: the reference's
+ * round-robin applied to block indices (main.cu:526-545); vranks = P >= 2 (nb divisible by 2P): the two-level
+ * tournament the multi-GPU ring walks, which the single-GPU solver uses with P = 4.  The
+ * reference has no block level; this replaces the role of its per-step pair lists (main.cu:971-990) for tests.
+ * Returns the number of pairs written, 0 for invalid arguments. */
+size_t svdj_block_schedule_step(size_t nb, int vranks, size_t step, size_t *pq);
+
 /* The solver keeps its work buffers (device and pinned) in a process-wide pool between calls, because
  * cudaMalloc / cudaFree synchronise the whole device and showed up as 100 ms stalls inside solves; the
  * reference allocates and frees its staging vectors on every call (main.cu:484-494, 1385-1392).

@@ -92,6 +92,7 @@ EXPORTS = (
     "svdj_ipc_close",
     "svdj_num_steps",
     "svdj_schedule_step",
+    "svdj_block_schedule_step",
     "svdj_last_error",
     "svdj_release_workspace",
     "svdj_version",
@@ -142,6 +143,8 @@ def _load() -> C.CDLL:
     lib.svdj_num_steps.restype = sz
     lib.svdj_schedule_step.argtypes = [sz, sz, C.POINTER(C.c_size_t)]
     lib.svdj_schedule_step.restype = sz
+    lib.svdj_block_schedule_step.argtypes = [sz, C.c_int, sz, C.POINTER(C.c_size_t)]
+    lib.svdj_block_schedule_step.restype = sz
     lib.svdj_release_workspace.argtypes = []
     lib.svdj_release_workspace.restype = i
     lib.svdj_last_error.argtypes = []
@@ -186,6 +189,14 @@ def schedule_step(n: int, step: int) -> np.ndarray:
     """Pairs (p, q), 0-based, of one round-robin step as an (n//2, 2) array."""
     buf = (C.c_size_t * (2 * max(n // 2, 1)))()
     cnt = lib.svdj_schedule_step(n, step, buf)
+    return np.array(buf[: 2 * cnt], dtype=np.int64).reshape(-1, 2)
+
+
+def block_schedule_step(nb: int, vranks: int, step: int) -> np.ndarray:
+    """Block pairs (p, q), 0-based, of one step of the block path's ordering over nb column blocks as an
+    (nb//2, 2) array; vranks >= 2 selects the two-level tournament (svdj.h: svdj_block_schedule_step)."""
+    buf = (C.c_size_t * (2 * max(nb // 2, 1)))()
+    cnt = lib.svdj_block_schedule_step(nb, vranks, step, buf)
     return np.array(buf[: 2 * cnt], dtype=np.int64).reshape(-1, 2)
 
 

@@ -531,6 +531,20 @@ size_t svdj_schedule_step(size_t n, size_t step, size_t *pq) {
   return pairs;
 }
 
+size_t svdj_block_schedule_step(size_t nb, int vranks, size_t step, size_t *pq) {
+  if (nb < 2 || nb > 0x7fffffffu || pq == nullptr || step >= svdj_num_steps(nb)) return 0;
+  const bool two_level = vranks >= 2 && nb % (2u * (size_t)vranks) == 0;
+  if (vranks >= 2 && !two_level) return 0;
+  const size_t pairs = nb / 2;
+  for (size_t i = 0; i < pairs; ++i) {
+    const Pair pr = two_level ? two_level_pair((unsigned)nb, (unsigned)vranks, (unsigned)step + 1u, (unsigned)i)
+                              : sameh_pair((unsigned)nb, (unsigned)step + 1u, (unsigned)i);
+    pq[2 * i] = pr.p;
+    pq[2 * i + 1] = pr.q;
+  }
+  return pairs;
+}
+
 size_t svdj_step_scratch_doubles(size_t m, size_t n) { return l1_scratch_doubles(m, n); }
 
 int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,

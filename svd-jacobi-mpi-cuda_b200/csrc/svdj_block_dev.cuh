@@ -82,31 +82,7 @@ __device__ __forceinline__ Pair block_pair(const BlockArgs &a, unsigned k, unsig
     r.q = half + (idx + k - 1u) % half;
     return r;
   }
-  const unsigned P = (unsigned)a.vranks, wb = a.nb / (2u * P);
-  const unsigned rk = idx / wb, li = idx - rk * wb;
-  Pair r;
-  if (k <= 2u * wb - 1u) {  // round 0: round-robin over the 2 wb blocks of super-blocks rk and P + rk
-    const Pair lp = sameh_pair(2u * wb, k, li);
-    r.p = (lp.p < wb ? rk : P + rk) * wb + (lp.p < wb ? lp.p : lp.p - wb);
-    r.q = (lp.q < wb ? rk : P + rk) * wb + (lp.q < wb ? lp.q : lp.q - wb);
-    if (r.p > r.q) { const unsigned t2 = r.p; r.p = r.q; r.q = t2; }
-    return r;
-  }
-  const unsigned rd = 1u + (k - 2u * wb) / wb, t = (k - 2u * wb) % wb;
-  // circle method: super-block 0 stays at top[0]; the other 2P-1 places form a ring
-  // top[1] -> ... -> top[P-1] -> bottom[P-1] -> ... -> bottom[0] -> top[1], everything moves one place per round
-  const unsigned ring = 2u * P - 1u;
-  auto occupant = [&](unsigned pos) {  // super-block that started at ring position pos
-    return pos < P - 1u ? pos + 1u : P + (2u * P - 2u - pos);
-  };
-  const unsigned top = (rk == 0u) ? 0u : occupant((rk - 1u + ring - rd % ring) % ring);
-  const unsigned bot = occupant((2u * P - 2u - rk + ring - rd % ring) % ring);
-  r.p = top * wb + li;
-  r.q = bot * wb + (li + t) % wb;
-  // lower block index first: the eigenvalue ordering then always sends the larger columns to the lower block,
-  // a consistent direction for every pair (a sorting network), whatever place the super-blocks are in
-  if (r.p > r.q) { const unsigned t2 = r.p; r.p = r.q; r.q = t2; }
-  return r;
+  return two_level_pair(a.nb, (unsigned)a.vranks, k, idx);
 }
 
 }  // namespace svdj

@@ -69,6 +69,41 @@ __host__ __device__ inline Pair sameh_pair(unsigned n, unsigned k, unsigned idx)
   return r;
 }
 
+// Two-level tournament over nb = 2 P wb blocks (P "virtual ranks"), the ordering the multi-GPU ring walks, as a
+// function of (step k = 1 .. nb-1, pair index idx = 0 .. nb/2-1).  The blocks form 2P super-blocks of wb blocks.
+// Steps 1 .. 2wb-1 (round 0): round-robin inside each pair of super-blocks (r, P + r).  Then rounds 1 .. 2P-2 of
+// wb steps each: the circle method moves the super-blocks one place (super-block 0 stays at top[0]; the other
+// 2P-1 places form the ring top[1] -> ... -> top[P-1] -> bottom[P-1] -> ... -> bottom[0] -> top[1]) and only the
+// pairs across the two super-blocks of a virtual rank are visited (block li of the top one with block
+// (li + t) mod wb of the bottom one).  Every block pair exactly once per nb-1 steps, nb/2 disjoint pairs per step.
+// The lower block index comes first.
+__host__ __device__ inline Pair two_level_pair(unsigned nb, unsigned P, unsigned k, unsigned idx) {
+  const unsigned wb = nb / (2u * P);
+  const unsigned rk = idx / wb, li = idx - rk * wb;
+  Pair r;
+  if (k <= 2u * wb - 1u) {
+    const Pair lp = sameh_pair(2u * wb, k, li);
+    r.p = (lp.p < wb ? rk : P + rk) * wb + (lp.p < wb ? lp.p : lp.p - wb);
+    r.q = (lp.q < wb ? rk : P + rk) * wb + (lp.q < wb ? lp.q : lp.q - wb);
+  } else {
+    const unsigned rd = 1u + (k - 2u * wb) / wb, t = (k - 2u * wb) % wb;
+    const unsigned ring = 2u * P - 1u;
+    const unsigned sh = ring - rd % ring;
+    const unsigned pt = (rk + ring - 1u + sh) % ring;           // ring position the occupant of top[rk] started at
+    const unsigned pb = (2u * P - 2u - rk + sh) % ring;         // ... of bottom[rk]
+    const unsigned top = (rk == 0u) ? 0u : (pt < P - 1u ? pt + 1u : P + (2u * P - 2u - pt));
+    const unsigned bot = pb < P - 1u ? pb + 1u : P + (2u * P - 2u - pb);
+    r.p = top * wb + li;
+    r.q = bot * wb + (li + t) % wb;
+  }
+  if (r.p > r.q) {
+    const unsigned t2 = r.p;
+    r.p = r.q;
+    r.q = t2;
+  }
+  return r;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Rotation parameters from the Gram triple; restates lib/JacobiMethods.cu:464-477.
 // alpha = a_p.a_q, beta = |a_p|^2, gamma = |a_q|^2.  Returns false when the pair is left alone.

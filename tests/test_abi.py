@@ -41,6 +41,59 @@ def test_schedule_matches_oracle(svdj, n):
     assert len(svdj.schedule_step(n, svdj.num_steps(n))) == 0  # past the last step
 
 
+@pytest.mark.parametrize("nb,vranks", [(4, 1), (4, 2), (8, 2), (16, 4), (24, 3), (64, 8), (128, 4), (128, 2), (256, 4), (12, 2), (9, 0)])
+def test_block_schedule_visits_every_block_pair_once(svdj, nb, vranks):
+    """The block path's orderings (flat round-robin and the two-level tournament): disjoint pairs in every step,
+    every unordered block pair exactly once per sweep -- the property the reference's ordering has for columns
+    (main.cu:498-545)."""
+    seen = set()
+    steps = svdj.num_steps(nb)
+    for k in range(steps):
+        pq = svdj.block_schedule_step(nb, vranks, k)
+        assert len(pq) == nb // 2
+        used = set()
+        for p, q in pq.tolist():
+            if p >= nb or q >= nb:   # odd nb: the idle block of the step is paired with the dummy index nb
+                continue
+            assert p != q and p not in used and q not in used
+            used |= {p, q}
+            key = (min(p, q), max(p, q))
+            assert key not in seen
+            seen.add(key)
+            if vranks >= 2:
+                assert p < q             # lower block first: the eigenvalue ordering needs a consistent direction
+    assert len(seen) == nb * (nb - 1) // 2
+
+
+def test_block_schedule_two_level_structure(svdj):
+    """Round 0 stays inside super-block pairs (r, P + r); later rounds only cross the two super-blocks one
+    virtual rank holds, and within a round every virtual rank keeps the same two super-blocks (what lets the
+    multi-GPU ring keep them resident for the round)."""
+    nb, P = 64, 4
+    wb = nb // (2 * P)
+    for k in range(2 * wb - 1):
+        for p, q in svdj.block_schedule_step(nb, P, k).tolist():
+            assert {p // wb, q // wb} <= {(p // wb) % P, (p // wb) % P + P}
+    k = 2 * wb - 1
+    while k < nb - 1:
+        held = None
+        for t in range(wb):
+            pq = svdj.block_schedule_step(nb, P, k + t)
+            sb = [tuple(sorted({p // wb, q // wb})) for p, q in pq.tolist()]
+            assert all(len(x) == 2 for x in sb)       # cross pairs only
+            by_rank = [sb[r * wb] for r in range(P)]
+            assert all(sb[r * wb + i] == by_rank[r] for r in range(P) for i in range(wb))
+            held = held or by_rank
+            assert by_rank == held
+        k += wb
+
+
+def test_block_schedule_rejects_bad_arguments(svdj):
+    assert len(svdj.block_schedule_step(10, 4, 0)) == 0     # 10 blocks do not split into 8 super-blocks
+    assert len(svdj.block_schedule_step(16, 4, 15)) == 0    # step out of range
+    assert len(svdj.block_schedule_step(1, 0, 0)) == 0
+
+
 def test_argument_errors_come_back_as_negative_argument_numbers(svdj):
     A = np.zeros((4, 4), order="F")
     s = np.zeros(4)

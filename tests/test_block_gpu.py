@@ -215,3 +215,54 @@ def test_block_width_32_option(svdj, m, n):
     # same answer as the default width
     A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
     assert st2.reserved == 16 and H.sigma_error_normwise(s, s2) <= 1e-12
+
+
+@pytest.mark.parametrize("vranks", ["0", "2", "4", "8"])
+@pytest.mark.parametrize("block", ["16", "32"])
+def test_block_orderings_reach_the_same_svd(svdj, monkeypatch, vranks, block):
+    """Flat round-robin over the column blocks (the reference's ordering one level up) and the two-level
+    tournament with 2, 4 or 8 virtual ranks: different rotation sequences, the same converged SVD."""
+    m = n = 1024
+    A0 = H.uniform_matrix(m, n, seed=77)
+    monkeypatch.setenv("SVDJ_VRANKS", vranks)
+    monkeypatch.setenv("SVDJ_BLOCK", block)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st.converged == 1 and st.reserved == int(block)
+    assert st.sweeps <= 18, st.sweeps
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * n * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+
+
+@pytest.mark.parametrize("m,n", [(512, 512), (700, 384), (2048, 256)])
+def test_gram_cache_changes_nothing_but_the_time(svdj, monkeypatch, m, n):
+    """64-column kernels with and without the cache of the blocks' Gram matrices: same sweeps (+-1), same SVD."""
+    A0 = H.normal_matrix(m, n, seed=5 * m + n)
+    monkeypatch.setenv("SVDJ_BLOCK", "32")
+    out = {}
+    for cache in ("1", "0"):
+        monkeypatch.setenv("SVDJ_GCACHE", cache)
+        out[cache] = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+        assert out[cache][3].converged == 1 and out[cache][3].reserved == 32
+    (A1, s1, V1, st1), (A2, s2, V2, st2) = out["1"], out["0"]
+    assert abs(st1.sweeps - st2.sweeps) <= 1
+    assert H.sigma_error_normwise(s1, s2) <= 1e-13
+    assert H.sigma_error_normwise(s1, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    bound = 10 * max(m, n) * H.EPS
+    for A, s, V in ((A1, s1, V1), (A2, s2, V2)):
+        q = H.svd_quality(A0, A, s, V)
+        assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+
+
+def test_tall_input_uses_wide_blocks_and_converges(svdj):
+    """m >= 8 n: 64-column blocks and three inner sweeps (the eigen-solve does not grow with m)."""
+    m, n = 20000, 256
+    A0 = H.normal_matrix(m, n, seed=3)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_AUTO)
+    assert st.variant == svdj.VARIANT_BLOCK and st.reserved == 32 and st.converged == 1
+    assert st.sweeps <= 10, st.sweeps
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * m * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
