@@ -45,6 +45,25 @@ __global__ void __launch_bounds__(256) k(double *out, int iters, double seed) {
       double b2[2] = {b4[0], b4[1]};
 #pragma unroll
       for (int i = 0; i < 16; ++i) dmma1688(acc[i], a4, b2);
+    } else if (MODE == 4) {  // even warps DMMA m8n8k4, odd warps DFMA: do the two pipes run side by side?
+      if ((threadIdx.x >> 5) & 1) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fma(acc[i][j], a8[j], b4[j]);
+      } else {
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+          for (int i = 0; i < 16; ++i) dmma884(acc[i][0], acc[i][1], a8[i & 7], b4[i & 3]);
+      }
+    } else if (MODE == 5) {  // every warp interleaves 16 DMMA with 32 DFMA
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        dmma884(acc[i][0], acc[i][1], a8[i & 7], b4[i & 3]);
+        acc[i][2] = fma(acc[i][2], a8[i & 7], b4[i & 3]);
+        acc[i][3] = fma(acc[i][3], a8[(i + 1) & 7], b4[i & 3]);
+      }
     } else {  // m16n8k16
 #pragma unroll
       for (int i = 0; i < 16; ++i) dmma16816(acc[i], a8, b4);
@@ -85,5 +104,8 @@ int main() {
   run<1>("DMMA m8n8k4", 16.0 * 8 * 8 * 4 * 2);
   run<2>("DMMA m16n8k8", 16.0 * 16 * 8 * 8 * 2);
   run<3>("DMMA m16n8k16", 16.0 * 16 * 8 * 16 * 2);
+  // mode 4: per iteration an even warp does 32 DMMA (16384 flop), an odd warp 64 DFMA (4096 flop): mean per warp
+  run<4>("DMMA|DFMA warps", 0.5 * (32.0 * 512 + 64.0 * 64));
+  run<5>("DMMA+DFMA mixed", 16.0 * 512 + 32.0 * 64);
   return 0;
 }
