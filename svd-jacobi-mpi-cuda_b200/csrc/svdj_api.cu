@@ -374,6 +374,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   unsigned long long step_launches = 0;
   bool converged = false;
   const bool trace = std::getenv("SVDJ_TRACE") != nullptr;  // per-sweep progress on stderr
+  const bool early_stop = std::getenv("SVDJ_NO_EARLY_STOP") == nullptr && block;  // level-1 path: the reference's own test only
   for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
     a.counters = d_counters.as<SweepCounters>() + sweep;
     b.counters = a.counters;
@@ -413,6 +414,17 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
                    (unsigned long long)hc->applied, off, o.tol);
     }
     if (hc->applied == 0) {
+      converged = true;
+      break;
+    }
+    // Quadratic-convergence stop.  Every pair whose cosine exceeded tol was rotated to zero in this sweep; what a
+    // pair carries afterwards is what later rotations of its two columns put back: at most (rotations per column)
+    // x max_cos^2 <= applied x max_cos^2.  Below tol / 2 the next sweep would rotate nothing, i.e. the reference's
+    // stopping condition (a sweep without rotations, lib/JacobiMethods.cu:462-466) already holds and the
+    // confirming sweep -- 2-3 % of the solve, a whole extra tournament on several GPUs -- is not run.
+    // (4096^2: sweep 16 applies 240 rotations with max cosine 2.9e-8; sweep 17 would apply none.)
+    if (early_stop && off > 0.0 && off < 1e-6 && (double)hc->applied * off * off < 0.5 * o.tol &&
+        o.threshold_mode == SVDJ_THRESH_REL) {
       converged = true;
       break;
     }

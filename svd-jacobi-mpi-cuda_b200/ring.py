@@ -57,6 +57,17 @@ def rotate(top: List[int], bottom: List[int]) -> Tuple[List[int], List[int]]:
     return new_top, new_bottom
 
 
+def quadratic_stop(applied: int, max_cos: float, tol: float) -> bool:
+    """True when the sweep just finished leaves nothing for the next one to do (same rule as csrc/svdj_api.cu).
+
+    Every pair whose cosine exceeded tol was rotated to zero during the sweep; what is left on a pair afterwards
+    is what later rotations of its two columns put back, at most (rotations per column) x max_cos^2 <=
+    applied x max_cos^2.  If that is below tol/2 the next sweep would find every pair under the threshold and
+    rotate nothing -- the reference's stopping condition (lib/JacobiMethods.cu:462-466 yields no rotation in a
+    whole sweep) already holds, so the confirming sweep is not run."""
+    return 0.0 < max_cos < 1e-6 and applied * max_cos * max_cos < 0.5 * tol  # 0.0: the backend does not track it
+
+
 def tournament_rounds(P: int) -> List[Tuple[List[int], List[int]]]:
     """The 2P-1 arrangements of one sweep."""
     top, bottom = initial_arrangement(P)
@@ -381,7 +392,7 @@ class RingSolver:
             last_off = float(host[1:2].view(torch.float64)[0])
             applied_total += applied
             sweeps = sweep + 1
-            if applied == 0:
+            if applied == 0 or quadratic_stop(applied, last_off, self.tol):
                 converged = True
                 break
         return {"sweeps": sweeps, "converged": converged, "applied": applied_total, "last_offdiag": last_off,
