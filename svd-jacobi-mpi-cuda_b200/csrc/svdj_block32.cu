@@ -225,24 +225,35 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       if (ti != tj) G0[c][r] = s;
     }
   }
-  for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
+  const bool cross = a.cross_only != 0;
+  if (!cross)  // the CROSS loop keeps W in registers and writes it out at the end
+    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
   if (tid == 0) fresh_max = 0ull;
   __syncthreads();
 
+  // One pass over the pairs this schedule visits (CROSS: one pair per thread): is there anything to rotate (the
+  // same test the steps apply), and the largest cosine of the fresh matrix (what lib/JacobiMethods.cu:462
+  // computes per pair), as max of alpha^2 / (beta gamma) with one square root per warp.
+  const double tol2 = a.tol * a.tol;
+  int any = 0;
   {
-    double mx = 0.0;
-    for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
-      const int r = i >> 6, c = i & 63;
-      if (r < c) {
-        const double grr = G0[r][r], gcc = G0[c][c];
-        const double den = sqrt(grr * gcc);
-        const double off = (den > 0.0 && grr > a.floor2 && gcc > a.floor2) ? fabs(G0[r][c]) / den : 0.0;
-        mx = fmax(mx, off);
+    double mx2 = 0.0;
+    auto look = [&](int r, int c) {
+      const double al = G0[r][c], be = G0[r][r], ga = G0[c][c];
+      if (be > a.floor2 && ga > a.floor2) {
+        any |= (al * al > tol2 * be * ga) ? 1 : 0;
+        mx2 = fmax(mx2, al * al / (be * ga));
       }
+    };
+    if (cross) {
+      look((int)(tid >> 5), 32 + (int)(tid & 31));
+    } else {
+      for (unsigned i = tid; i < kD64 * kD64; i += 1024)
+        if ((i >> 6) < (i & 63)) look((int)(i >> 6), (int)(i & 63));
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(mx));
+    for (int o = 16; o > 0; o >>= 1) mx2 = fmax(mx2, __shfl_xor_sync(0xffffffffu, mx2, o));
+    if (lane == 0) atomicMax(&fresh_max, (unsigned long long)__double_as_longlong(sqrt(mx2)));
   }
 
   // Systolic layout.  Rows and columns of G (and the columns of W) are kept in SLOT order: slot j and slot 32 + j
@@ -257,7 +268,6 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   // sweep uses FULL for its first step, which orthogonalises every block internally, and CROSS afterwards:
   // every column pair is then rotated once per sweep, as in the reference's ordering, instead of re-rotating
   // the 992 intra-block pairs in each of the sweep's steps.
-  const bool cross = a.cross_only != 0;
   const int nsteps = cross ? 32 : kD64 - 1;
   auto next_slot = [cross](int p) {
     if (cross) return p < 32 ? p : 32 + ((p - 32 + 31) & 31);
@@ -266,17 +276,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   int total_rot = 0;
   int cur = 0;
   const int w1 = tid >> 5, l2 = lane;
-  const double tol2 = a.tol * a.tol;
   const int nr_t = next_slot(w1), nr_b = next_slot(32 + w1), nc_t = next_slot(l2), nc_b = next_slot(32 + l2);
-  // anything to do at all?  (the same test the steps apply, on the fresh matrix)
-  int any = 0;
-  for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
-    const int r = i >> 6, c = i & 63;
-    if (r < c && (!cross || (r < 32 && c >= 32))) {  // only the pairs this schedule visits
-      const double al = G0[r][c], be = G0[r][r], ga = G0[c][c];
-      any |= (al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2) ? 1 : 0;
-    }
-  }
   if (cross && tid < 32) {  // rotation inputs of the first CROSS step
     rin_al[tid] = G0[tid][32 + tid];
     rin_be[tid] = G0[tid][tid];
@@ -350,6 +350,10 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     W[w1][32 + l2] = wq0;
     W[w1 + 32][l2] = wp1;
     W[w1 + 32][32 + l2] = wq1;
+    __syncthreads();
+  }
+  if (cross && !any && a.force_update) {  // W = I still moves the columns (last step of a ring round)
+    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
     __syncthreads();
   }
   for (int sw = 0; sw < ((any && !cross) ? a.max_inner_sweeps : 0); ++sw) {
@@ -430,31 +434,29 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       valid[tid] = slot_col32(bp.p, bp.q, tid, a.n) != kNoCol;
     }
     __syncthreads();
-    const int all_valid = __syncthreads_and(tid >= kD64 || valid[tid]);
-    if (tid < kD64) {  // output slot of column tid: eigenvalues descending over the valid slots (single GPU only)
-      int out = tid;
-      if (a.sort_cols && valid[tid]) {
-        const double di = Gc[tid][tid];
-        int rk = 0;
-        for (int j = 0; j < kD64; ++j) {
-          const double dj = Gc[j][j];
-          rk += (valid[j] && (dj > di || (dj == di && j < (int)tid))) ? 1 : 0;
-        }
-        out = rk;
-        if (!all_valid) {  // ragged last block: the rk-th valid slot
-          int seen = 0;
-          for (int j = 0; j < kD64; ++j) {
-            if (valid[j]) {
-              if (seen == rk) {
-                out = j;
-                break;
-              }
-              ++seen;
-            }
+    {
+      // output slot of every column: eigenvalues descending over the valid slots (single GPU only).  Warp w ranks
+      // columns w and 32 + w: lane j compares them with columns j and 32 + j, two ballots each.
+      const int w = tid >> 5;
+      const double dj0 = Gc[lane][lane], dj1 = Gc[32 + lane][32 + lane];
+      const bool v0 = valid[lane] != 0, v1 = valid[32 + lane] != 0;
+      const unsigned vm0 = __ballot_sync(0xffffffffu, v0), vm1 = __ballot_sync(0xffffffffu, v1);
+#pragma unroll
+      for (int hsel = 0; hsel < 2; ++hsel) {
+        const int i = w + 32 * hsel;
+        const double di = Gc[i][i];
+        const unsigned b0 = __ballot_sync(0xffffffffu, v0 && (dj0 > di || (dj0 == di && (int)lane < i)));
+        const unsigned b1 = __ballot_sync(0xffffffffu, v1 && (dj1 > di || (dj1 == di && 32 + (int)lane < i)));
+        if (lane == 0) {
+          int out = i;
+          if (a.sort_cols && valid[i]) {
+            const int rk = __popc(b0) + __popc(b1);
+            const int n0 = __popc(vm0);  // the rk-th valid slot (ragged last block: not every slot is one)
+            out = rk < n0 ? (int)__fns(vm0, 0, rk + 1) : 32 + (int)__fns(vm1, 0, rk - n0 + 1);
           }
+          rank_of[i] = out;
         }
       }
-      rank_of[tid] = out;
     }
     __syncthreads();
     if (a.gcache != nullptr) {  // the rotated diagonal blocks, in the order the columns are written back in
