@@ -233,8 +233,9 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (block) {
     // sized for either block width (the 32-wide kernels need more of everything per pair, for half the pairs)
     size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
-    blk_scratch_sizes(m, n, &gp, &wd, &fl);
-    blk32_scratch_sizes(m, n, &gp2, &wd2, &fl2);
+    // (n + 256: room for the empty blocks the schedule may add, see below)
+    blk_scratch_sizes(m, n + 256, &gp, &wd, &fl);
+    blk32_scratch_sizes(m, n + 256, &gp2, &wd2, &fl2);
     gp = std::max(gp, gp2);
     wd = std::max(wd, wd2);
     fl = std::max(fl, fl2);
@@ -242,7 +243,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
     if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
     // per column block of 32: its Gram matrix as the last eigen-solve left it (8 KiB per block)
-    if (int rc = d_gcache.alloc(sizeof(double) * 1024 * (size_t)((n + 31) / 32 + 1))) return rc;
+    if (int rc = d_gcache.alloc(sizeof(double) * 1024 * (size_t)((n + 31) / 32 + 9))) return rc;
   } else if (l1_uses_split(m, n)) {
     if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
   }
@@ -272,7 +273,15 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
       wide = blk32_supported(probe_args);
     }
   }
-  const unsigned nb = wide ? blk32_num_blocks(n) : blk_num_blocks(n);
+  // Empty blocks at the end (all their column slots past n: the kernels treat them like the missing columns of a
+  // ragged last block) make the number of blocks even, so that every block is in a pair of the sweep's first step
+  // (cross-only inner schedule, Gram cache), and from 64 blocks on a multiple of 8, so that the two-level
+  // ordering applies whatever n is.  At most 7 extra blocks of 64+: they cost a Gram pass over zeros, no update.
+  unsigned nb = wide ? blk32_num_blocks(n) : blk_num_blocks(n);
+  if (block && std::getenv("SVDJ_NO_PAD") == nullptr) {
+    if (nb >= 64) nb = (nb + 7u) & ~7u;
+    else if (nb > 2 && (nb & 1u)) nb += 1u;
+  }
   const unsigned steps = (unsigned)svdj_num_steps(block ? nb : n);
   // column pairs looked at per step: n/2 on the level-1 path, 496 (b = 16) or 2016 (b = 32) per block pair
   const unsigned long long pairs_per_step =

@@ -737,8 +737,8 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   // first step of a sweep or ring phase: full eigen-solve (every block is in exactly one pair when their number is
   // even); later steps, and every step of the ring's bipartite CROSS phase: cross pairs only
   a.cross_only = (!blk_full_inner() && (a.sched == 1 || (k > 1 && a.nb % 2 == 0))) ? 1 : 0;
-  // The Gram cache needs whole blocks and every block in a pair of the first step, which refreshes it
-  if (a.gcache != nullptr && (a.n % kB32 != 0 || a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
+  // The Gram cache needs every block in a pair of the first step, which refreshes it
+  if (a.gcache != nullptr && (a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
   a.gram_mode = (a.gcache == nullptr) ? 0 : (k == 1 ? 1 : 2);
   static const cudaError_t attrs = [] {
     cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
