@@ -74,6 +74,8 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
     const unsigned c = slot_col32(bp.p, bp.q, warp + 4 * i, a.n);
     cptr[i] = (c != kNoCol) ? col_ptr(a, true, c) : nullptr;
   }
+  griddep_launch();
+  griddep_wait();  // the columns come from the previous step's update kernel
   auto issue_tile = [&](unsigned t, int stage) {
     const unsigned row = r0 + t * kG32Rows + 2 * lane;
     double *dst = tiles + stage * kG32TileDoubles + 2 * lane;
@@ -188,6 +190,8 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   const unsigned tid = threadIdx.x, lane = tid & 31;
   const unsigned pair = blockIdx.x;
 
+  griddep_launch();
+  griddep_wait();  // the partial Gram matrices come from K1
   const double *src = gpart + (size_t)pair * splits * kGramPart32;
   const bool cached = a.gcache != nullptr && a.gram_mode == 2;
   if (cached) {
@@ -528,6 +532,8 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned g = lane >> 2, tg = lane & 3;
 
+  griddep_launch();
+  griddep_wait();  // W and the flags come from K2
   if (warp == 0) {
     unsigned cnt = 0;
     for (unsigned base = 0; base < pairs; base += 32) {
@@ -767,16 +773,41 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
     return e ? std::atoi(e) : 3;
   }();
   if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  if (a.gram_mode == 2)
-    blk32_gram_kernel<true><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
-  else
-    blk32_gram_kernel<false><<<dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st>>>(a, k, rps, gpart);
+  static const bool use_pdl = [] {
+    const char *e = std::getenv("SVDJ_PDL");
+    return e != nullptr && e[0] == '1';
+  }();
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  auto cfg = [&](dim3 grid, unsigned block, size_t smem) {
+    cudaLaunchConfig_t c = {};
+    c.gridDim = grid;
+    c.blockDim = dim3(block);
+    c.dynamicSmemBytes = smem;
+    c.stream = st;
+    c.attrs = pdl_attr;
+    c.numAttrs = use_pdl ? 1 : 0;
+    return c;
+  };
+  {
+    cudaLaunchConfig_t c = cfg(dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles);
+    if (a.gram_mode == 2) SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_gram_kernel<true>, a, k, rps, gpart));
+    else SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_gram_kernel<false>, a, k, rps, gpart));
+  }
   if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  blk32_eig_kernel<<<pairs, 1024, kE32Smem, st>>>(a, k, splits, gpart, wbuf, wflag);
+  {
+    cudaLaunchConfig_t c = cfg(dim3(pairs), 1024, kE32Smem);
+    SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_eig_kernel, a, k, splits, (const double *)gpart, wbuf, wflag));
+  }
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  blk32_update_kernel<<<sm_count * kU32CtasPerSm, kU32Threads, kU32Smem, st>>>(a, k, wbuf, wflag, pairs, probe ? probe->active_pairs : nullptr);
+  {
+    cudaLaunchConfig_t c = cfg(dim3(sm_count * kU32CtasPerSm), kU32Threads, kU32Smem);
+    SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_update_kernel, a, k, (const double *)wbuf, (const int *)wflag, pairs,
+                                     probe ? probe->active_pairs : (unsigned long long *)nullptr));
+  }
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());

@@ -37,6 +37,13 @@ __device__ __forceinline__ void fast_rotation(double alpha, double beta, double 
 }
 
 
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-serialization attribute may start
+// while its predecessor in the stream is still draining; griddep_wait() returns once the predecessor has completed
+// and its memory is visible, griddep_launch() lets the successor's CTAs be scheduled as soon as SM resources free
+// up.  Everything before griddep_wait() must not touch global memory the predecessor reads or writes.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, int src_bytes) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem_src), "r"(src_bytes) : "memory");

@@ -266,3 +266,25 @@ def test_tall_input_uses_wide_blocks_and_converges(svdj):
     q = H.svd_quality(A0, A, s, V)
     bound = 10 * m * H.EPS
     assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+
+
+def test_quadratic_stop_saves_the_confirming_sweep_only(svdj, monkeypatch):
+    """With and without the quadratic-convergence stop: at most one sweep apart, the same SVD, and the state the
+    early stop leaves passes the reference's test (a further solve on the result rotates nothing)."""
+    m = n = 768
+    A0 = H.uniform_matrix(m, n, seed=21)
+    A1, s1, V1, st1 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    monkeypatch.setenv("SVDJ_NO_EARLY_STOP", "1")
+    A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
+    assert st1.converged == 1 and st2.converged == 1
+    assert st2.sweeps - st1.sweeps in (0, 1)
+    assert st2.last_offdiag <= m * 2.0 ** -53 * (1 + 1e-9)     # the confirming sweep saw nothing above tol
+    assert H.sigma_error_normwise(s1, s2) <= 1e-14
+    q = H.svd_quality(A0, A1, s1, V1)
+    bound = 10 * n * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+    # U * diag(s) from the early stop is already orthogonal to working accuracy: solving it again applies nothing
+    B = np.asfortranarray(A1 * s1)
+    s3 = np.zeros(n); V3 = np.zeros((n, n), order="F")
+    st3 = svdj.dgesvd(svdj.AllVec, svdj.AllVec, m, n, B, m, s3, V3, n, svdj.default_opts(variant=svdj.VARIANT_BLOCK))
+    assert st3.sweeps == 1 and st3.applied == 0

@@ -179,3 +179,15 @@ def test_buffer_roles_follow_the_tournament(P):
             assert sorted([new[q]["top"], new[q]["bottom"]] + new[q]["spare"]) == [0, 1, 2, 3]
         roles = new
         held = [{new[q]["top"]: top[q], new[q]["bottom"]: bot[q]} for q in range(P)]
+
+
+def test_quadratic_stop_rule():
+    """The confirming sweep is skipped only when what the sweep can have left behind is below tol/2."""
+    from importlib import import_module
+    ring = import_module("svd-jacobi-mpi-cuda_b200.ring")
+    tol = 4096 * 2.0 ** -53
+    assert ring.quadratic_stop(240, 2.87e-8, tol)           # the 4096^2 case: 240 x 8.2e-16 = 2.0e-13 < 2.3e-13
+    assert not ring.quadratic_stop(2657, 1.2e-2, tol)       # still far from converged
+    assert not ring.quadratic_stop(2153, 1.8e-7, 20000 * 2.0 ** -53)  # 7e-11 > tol / 2
+    assert not ring.quadratic_stop(10, 0.0, tol)            # a backend that does not track the cosine never stops early
+    assert not ring.quadratic_stop(1, 2e-6, 1.0)            # the cosine itself must be small
