@@ -41,6 +41,8 @@ template <int WARPS, int UNROLL>
 __global__ void __launch_bounds__(WARPS * 32) blk_gram_kernel(const BlockArgs a, const unsigned k,
                                                               const unsigned rows_per_split,
                                                               double *__restrict__ gpart) {
+  griddep_launch();
+  griddep_wait();  // everything this kernel reads comes from the kernel before it in the stream
   __shared__ double red[WARPS][kGramPart];
   const Pair bp = block_pair(a, k, blockIdx.x);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -124,6 +126,8 @@ __device__ __forceinline__ void circle_pair(int t, int j, int &p, int &q) {
 __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
                                                       const double *__restrict__ gpart, double *__restrict__ wbuf,
                                                       int *__restrict__ wflag) {
+  griddep_launch();
+  griddep_wait();  // everything this kernel reads comes from the kernel before it in the stream
   // Row stride kD + 2: the rotation inputs G[p][q] of a step satisfy p + q = const (circle method), so their
   // addresses are (stride - 1) p + const; an odd (stride - 1) spreads them over the banks (stride kD + 1 put
   // all sixteen pairs on one bank), and the diagonal, (stride + 1) p, stays conflict-free as well.
@@ -314,6 +318,8 @@ __global__ void __launch_bounds__(WARPS * 32) blk_update_kernel(const BlockArgs 
                                                                 const double *__restrict__ wbuf,
                                                                 const int *__restrict__ wflag,
                                                                 unsigned long long *__restrict__ active_out) {
+  griddep_launch();
+  griddep_wait();  // everything this kernel reads comes from the kernel before it in the stream
   if (active_out != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
     unsigned cnt = 0;
     for (unsigned p = 0; p < gridDim.x; ++p) cnt += wflag[p] != 0;
@@ -409,6 +415,8 @@ __global__ void __launch_bounds__(128, kUpdCtasPerSm) blk_update_staged_kernel(c
                                                                   const int *__restrict__ wflag,
                                                                   const unsigned pairs,
                                                                   unsigned long long *__restrict__ active_out) {
+  griddep_launch();
+  griddep_wait();  // everything this kernel reads comes from the kernel before it in the stream
   extern __shared__ __align__(16) double tiles[];  // STAGES x 32 columns x kTileStride
   __shared__ unsigned short active[kMaxCompactPairs];
   __shared__ unsigned n_active_s;
@@ -551,6 +559,8 @@ template <int STAGES>
 __global__ void __launch_bounds__(128) blk_gram_staged_kernel(const BlockArgs a, const unsigned k,
                                                               const unsigned rows_per_split,
                                                               double *__restrict__ gpart) {
+  griddep_launch();
+  griddep_wait();  // everything this kernel reads comes from the kernel before it in the stream
   extern __shared__ __align__(16) double tiles[];  // STAGES x 32 columns x kTileStride; reused for the reduction
   const Pair bp = block_pair(a, k, blockIdx.x);
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -715,11 +725,11 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
                                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStageSmem);
     SVDJ_CUDA_TRY(gattr);
     rps = (rps + kTileRows - 1) / kTileRows * kTileRows;  // whole tiles per split
-    blk_gram_staged_kernel<kUpdStages><<<dim3(pairs, splits), 128, kStageSmem, st>>>(a, k, rps, gpart);
+    SVDJ_CUDA_TRY(launch_k(blk_gram_staged_kernel<kUpdStages>, dim3(pairs, splits), 128, kStageSmem, st, a, k, rps, gpart));
   } else {
-    blk_gram_kernel<kGramWarps, kGramUnroll><<<dim3(pairs, splits), kGramWarps * 32, 0, st>>>(a, k, rps, gpart);
+    SVDJ_CUDA_TRY(launch_k(blk_gram_kernel<kGramWarps, kGramUnroll>, dim3(pairs, splits), kGramWarps * 32, 0, st, a, k, rps, gpart));
   }
-  blk_eig_kernel<<<pairs, 256, 0, st>>>(a, k, splits, gpart, wbuf, wflag);
+  SVDJ_CUDA_TRY(launch_k(blk_eig_kernel, dim3(pairs), 256, 0, st, a, k, splits, gpart, wbuf, wflag));
   const unsigned strips = ((a.m + 7) >> 3) + (a.rotate_v ? ((a.vrows + 7) >> 3) : 0);
   unsigned usplits = (8 * 148 + pairs - 1) / pairs;
   const unsigned ucap = (strips + kUpdWarps * 4 - 1) / (kUpdWarps * 4);  // >= 4 strips per warp
@@ -736,13 +746,13 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
                                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     SVDJ_CUDA_TRY(attr);
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-    blk_update_staged_kernel<kUpdStages><<<sm_count * kUpdCtasPerSm, 128, smem, st>>>(a, k, wbuf, wflag, pairs,
-                                                                          probe ? probe->active_pairs : nullptr);
+    SVDJ_CUDA_TRY(launch_k(blk_update_staged_kernel<kUpdStages>, dim3(sm_count * kUpdCtasPerSm), 128, smem, st, a, k, wbuf,
+                           wflag, pairs, probe ? probe->active_pairs : nullptr));
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   } else {
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-    blk_update_kernel<kUpdWarps><<<dim3(pairs, usplits), kUpdWarps * 32, 0, st>>>(a, k, wbuf, wflag,
-                                                                                  probe ? probe->active_pairs : nullptr);
+    SVDJ_CUDA_TRY(launch_k(blk_update_kernel<kUpdWarps>, dim3(pairs, usplits), kUpdWarps * 32, 0, st, a, k, wbuf, wflag,
+                           probe ? probe->active_pairs : nullptr));
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   }
   if (launches) *launches += 3;

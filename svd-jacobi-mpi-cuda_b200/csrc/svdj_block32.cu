@@ -773,41 +773,17 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
     return e ? std::atoi(e) : 3;
   }();
   if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  static const bool use_pdl = [] {
-    const char *e = std::getenv("SVDJ_PDL");
-    return e != nullptr && e[0] == '1';
-  }();
-  cudaLaunchAttribute pdl_attr[1];
-  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
-  auto cfg = [&](dim3 grid, unsigned block, size_t smem) {
-    cudaLaunchConfig_t c = {};
-    c.gridDim = grid;
-    c.blockDim = dim3(block);
-    c.dynamicSmemBytes = smem;
-    c.stream = st;
-    c.attrs = pdl_attr;
-    c.numAttrs = use_pdl ? 1 : 0;
-    return c;
-  };
-  {
-    cudaLaunchConfig_t c = cfg(dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles);
-    if (a.gram_mode == 2) SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_gram_kernel<true>, a, k, rps, gpart));
-    else SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_gram_kernel<false>, a, k, rps, gpart));
-  }
+  if (a.gram_mode == 2)
+    SVDJ_CUDA_TRY(launch_k(blk32_gram_kernel<true>, dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st, a, k, rps, gpart));
+  else
+    SVDJ_CUDA_TRY(launch_k(blk32_gram_kernel<false>, dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st, a, k, rps, gpart));
   if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  {
-    cudaLaunchConfig_t c = cfg(dim3(pairs), 1024, kE32Smem);
-    SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_eig_kernel, a, k, splits, (const double *)gpart, wbuf, wflag));
-  }
+  SVDJ_CUDA_TRY(launch_k(blk32_eig_kernel, dim3(pairs), 1024, kE32Smem, st, a, k, splits, gpart, wbuf, wflag));
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  {
-    cudaLaunchConfig_t c = cfg(dim3(sm_count * kU32CtasPerSm), kU32Threads, kU32Smem);
-    SVDJ_CUDA_TRY(cudaLaunchKernelEx(&c, blk32_update_kernel, a, k, (const double *)wbuf, (const int *)wflag, pairs,
-                                     probe ? probe->active_pairs : (unsigned long long *)nullptr));
-  }
+  SVDJ_CUDA_TRY(launch_k(blk32_update_kernel, dim3(sm_count * kU32CtasPerSm), kU32Threads, kU32Smem, st, a, k, wbuf, wflag, pairs,
+                         probe ? probe->active_pairs : nullptr));
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (launches) *launches += 3;
   SVDJ_CUDA_TRY(cudaGetLastError());

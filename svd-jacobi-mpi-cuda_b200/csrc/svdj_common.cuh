@@ -2,6 +2,8 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <cstdlib>
+#include <utility>
 #include <stddef.h>
 #include <stdint.h>
 
@@ -239,6 +241,32 @@ struct BlockArgs {
 };
 // Optional timing of the update kernel (the dominant, HBM-bound one) of a step: events recorded around it
 // and a device counter that receives the number of block pairs it really updated.
+// Kernel launch with the programmatic-dependent-launch attribute (on unless SVDJ_PDL=0): the next kernel of the
+// stream may be scheduled while this one drains; the kernels order themselves with griddepcontrol.wait
+// (svdj_block_dev.cuh).  Measured: 385 -> 372 ms at 4096^2, 80 -> 75 ms at 2048^2.
+inline bool pdl_enabled() {
+  static const bool on = [] {
+    const char *e = std::getenv("SVDJ_PDL");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, unsigned block, size_t smem, cudaStream_t st,
+                            Args &&...args) {
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t c = {};
+  c.gridDim = grid;
+  c.blockDim = dim3(block);
+  c.dynamicSmemBytes = smem;
+  c.stream = st;
+  c.attrs = attr;
+  c.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&c, kern, std::forward<Args>(args)...);
+}
+
 struct BlockProbe {
   cudaEvent_t before = nullptr, after = nullptr;
   unsigned long long *active_pairs = nullptr;
