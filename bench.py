@@ -311,6 +311,130 @@ def run_ring(args, svdj, world, rank, local_rank):
     return 0
 
 
+def run_rows(args, svdj, world, rank, local_rank):
+    """--rows M with M >= 8 n: the tall-skinny workload (BASELINE.json config 4 is 1048576 x 512), sharded by rows
+    over the N GPUs (svd-jacobi-mpi-cuda_b200/rows.py): one all-reduce of the Gram matrices per step, no column
+    traffic.  Strong scaling: the matrix is the same for every N (generated in 65536-row chunks, seed per chunk)."""
+    import torch
+    import torch.distributed as dist
+
+    rows = importlib.import_module("svd-jacobi-mpi-cuda_b200.rows")
+    m, n = args.rows, args.n
+    dev = torch.device("cuda", local_rank)
+    solver = rows.RowShardSolver(m, n, dev)
+    r0, ml = solver.row0, solver.m_local
+
+    def my_rows():  # (n, m_local), standard normal, the same global matrix whatever the partition
+        CH = 65536
+        out = torch.empty(n, ml, dtype=torch.float64, device=dev)
+        for c in range(r0 // CH, (r0 + ml - 1) // CH + 1):
+            g = torch.Generator(device=dev)
+            g.manual_seed(1234 + c)
+            chunk = torch.randn(n, min(CH, m - c * CH), dtype=torch.float64, device=dev, generator=g)
+            lo, hi = max(r0, c * CH), min(r0 + ml, (c + 1) * CH)
+            out[:, lo - r0:hi - r0] = chunk[:, lo - c * CH:hi - c * CH]
+        return out
+
+    A_rows = my_rows()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_solve():
+        solver.fill_local(A_rows)
+        return solver.solve()
+
+    for _ in range(args.warmup):
+        one_solve()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    solver.allreduce_calls = solver.allreduce_bytes = 0
+    stats = []
+    ev0.record()
+    for _ in range(args.steps):
+        stats.append(one_solve())
+    ev1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ev0.elapsed_time(ev1) * 1e-3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    per_step_s = float(t.item()) / args.steps
+    st = stats[-1]
+
+    # e2e: every rank's rows start in its own pinned host memory and its rows of U and V (and sigma) end there
+    hA = A_rows.cpu().pin_memory()
+    hU = torch.empty(n, ml, dtype=torch.float64).pin_memory()
+    hV = torch.empty(n, solver.v_local, dtype=torch.float64).pin_memory()
+    hs = torch.empty(n, dtype=torch.float64).pin_memory()
+    e2e = []
+    for it in range(1 + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        solver.fill_local(hA.to(dev, non_blocking=True))
+        solver.solve()
+        hU.copy_(solver.U_local, non_blocking=True)
+        hV.copy_(solver.V_local, non_blocking=True)
+        hs.copy_(solver.sigma, non_blocking=True)
+        barrier()
+        if it > 0:
+            e2e.append(time.perf_counter() - t0)
+    e2e_s = float(np.mean(e2e))
+
+    # accuracy from the row slices: U^T U and V^T V are sums over the ranks; the residual needs the whole (small) V
+    U, V, sg = solver.U_local.T, solver.V_local.T, solver.sigma        # (m_local, n), (v_local, n)
+    utu, vtv = U.T @ U, V.T @ V
+    Vfull = torch.zeros(n, n, dtype=torch.float64, device=dev)
+    Vfull[solver.v_row0:solver.v_row0 + solver.v_local] = V
+    if world > 1:
+        dist.all_reduce(utu)
+        dist.all_reduce(vtv)
+        dist.all_reduce(Vfull)
+    res2 = torch.stack([torch.linalg.norm(A_rows.T - (U * sg) @ Vfull.T) ** 2, torch.linalg.norm(A_rows) ** 2])
+    if world > 1:
+        dist.all_reduce(res2)
+    if rank == 0:
+        eye = torch.eye(n, dtype=torch.float64, device=dev)
+        acc = {"orth_u": float((utu - eye).abs().max()), "orth_v": float((vtv - eye).abs().max()),
+               "resid": float(torch.sqrt(res2[0] / res2[1])), "bound_10_m_eps": 10 * m * 2.0 ** -52}
+        launches = sum(s_.step_kernel_launches for s_ in stats)
+        pairs_upd = sum(s_.probe_block_pairs for s_ in stats)
+        k_ms = float(np.mean([s_.step_kernel_ms for s_ in stats]))
+        flops_per_launch = pairs_upd * 2.0 * (ml + solver.v_local) * 64 * 64 / max(launches, 1)
+        tfs = flops_per_launch / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
+        line = {
+            "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{m}x{n} dense N(0,1) FP64, full SVD (U, S, V) to convergence",
+                       "variant": "block", "block_width": 32, "tol": "m*2^-53 relative",
+                       "l2": "inputs_larger_than_l2 (A = %d MiB)" % (m * n * 8 >> 20),
+                       "parallelism": f"rows sharded over {world} GPU(s): {ml} rows of A and {solver.v_local} rows of V "
+                                      "per rank, one all-reduce of the block pairs' Gram matrices per step"},
+            "sweeps": st.sweeps, "rotations_applied": int(st.applied),
+            "rows": {"allreduce_calls_per_solve": solver.allreduce_calls / args.steps,
+                     "allreduce_bytes_per_solve": solver.allreduce_bytes / args.steps},
+            "roofline": {"bound": "tensor", "achieved": tfs, "peak": 36.9, "unit": "TFLOP/s", "frac": tfs / 36.9,
+                         "traffic": None, "kernel": "blk32_update_kernel on rank 0's rows",
+                         "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md",
+                         "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
+                         "launches_probed": int(launches)},
+            "cpu_baseline": None,
+            "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
+                    "d2h_bytes_per_step": (m * n + n * n + n) * 8},
+            "gpu_launches": int(sum(s_.launches for s_ in stats)) * world, "clocks": clocks, "accuracy": acc,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def run_svdj(args):
     import torch
     import torch.distributed as dist
@@ -326,6 +450,10 @@ def run_svdj(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    if args.rows:
+        if args.rows < 8 * args.n:
+            raise SystemExit("--rows M is the tall-skinny workload: M >= 8 * --size")
+        return run_rows(args, svdj, world, rank, local_rank)
     if world > 1:
         return run_ring(args, svdj, world, rank, local_rank)
 
@@ -493,6 +621,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="svdj", choices=["svdj", "reference"])
     ap.add_argument("--size", "--n", dest="n", type=int, default=4096)
+    ap.add_argument("--rows", type=int, default=0, help="M >= 8 * size: the tall M x size workload, sharded by rows over the GPUs")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"], help="N > 1: how column blocks move")

@@ -202,6 +202,22 @@ int svdj_ipc_export(void *dptr, unsigned char *handle64);
 int svdj_ipc_open(const unsigned char *handle64, void **peer_ptr);
 int svdj_ipc_close(void *peer_ptr);
 
+/* Row-sharded solve for tall inputs on several GPUs ("Tall-skinny"): every rank -- one process
+ * per GPU -- holds m_local rows of A (all n columns, column-major, lda >= m_local) and rows v_row0 ..
+ * v_row0 + vrows_local - 1 of V (ldv >= vrows_local); the row slices of the ranks tile A and V.  All ranks call
+ * with the same n, opts and job flags.  The only quantity a step needs from the other ranks is the Gram matrices
+ * of its block pairs: `allreduce(ctx, dptr, count, stream)` must sum `count` doubles at device pointer `dptr` over
+ * all ranks, in place, ordered on `stream` (e.g. ncclAllReduce / torch.distributed.all_reduce), and return 0.
+ * Every rank then runs the same eigen-solves and updates its own rows; sigma comes out complete on every rank, U
+ * and V as the caller's row slices.  opts->tol must be set (m_global * 2^-53 for the library default).  n >= 128,
+ * 16-byte aligned columns and even leading dimensions are required (SVDJ_ERR_UNSUPPORTED otherwise).
+ * Replaces, for m >> n, the reference's distribution of a step's pairs over MPI ranks through rank 0
+ * (main.cu:583-942): there every rank needs whole columns of m doubles per pair, here 18 KiB per block pair. */
+typedef int (*svdj_allreduce_fn)(void *ctx, double *dptr, size_t count, void *stream);
+int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double *dA, size_t lda, double *ds,
+                            double *dV, size_t ldv, size_t vrows_local, size_t v_row0, const svdj_opts *opts,
+                            svdj_stats *stats, void *stream, svdj_allreduce_fn allreduce, void *ctx);
+
 /* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
 size_t svdj_num_steps(size_t n);
 

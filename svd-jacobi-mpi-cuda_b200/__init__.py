@@ -35,6 +35,10 @@ class SvdjError(RuntimeError):
         self.code = code
 
 
+# svdj_allreduce_fn (svdj.h): sum `count` doubles at device pointer `dptr` over all ranks, in place, on `stream`
+AllreduceFn = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
+
+
 class Opts(C.Structure):
     _fields_ = [
         ("tol", C.c_double),
@@ -93,6 +97,7 @@ EXPORTS = (
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_block_schedule_step",
+    "svdj_dgesvd_rows_device",
     "svdj_last_error",
     "svdj_release_workspace",
     "svdj_version",
@@ -145,6 +150,9 @@ def _load() -> C.CDLL:
     lib.svdj_schedule_step.restype = sz
     lib.svdj_block_schedule_step.argtypes = [sz, C.c_int, sz, C.POINTER(C.c_size_t)]
     lib.svdj_block_schedule_step.restype = sz
+    lib.svdj_dgesvd_rows_device.argtypes = [C.c_int, C.c_int, sz, sz, C.c_void_p, sz, C.c_void_p, C.c_void_p, sz, sz, sz,
+                                            C.POINTER(Opts), C.POINTER(Stats), C.c_void_p, AllreduceFn, C.c_void_p]
+    lib.svdj_dgesvd_rows_device.restype = C.c_int
     lib.svdj_release_workspace.argtypes = []
     lib.svdj_release_workspace.restype = i
     lib.svdj_last_error.argtypes = []

@@ -198,9 +198,17 @@ static int check_args(int jobu, int jobv, size_t m, size_t n, const double *A, s
 
 // The sweep loop + finalisation on device-resident buffers.
 // vrows: rows of V the kernels rotate (n, or n rounded up to even when the buffer has a zero pad row).
+// rs != nullptr: row-sharded solve (svdj_dgesvd_rows_device): m and vrows are this rank's rows of A and V,
+// v_row0 the first row of V it holds, rs->fn the all-reduce over the ranks
+struct RowShard {
+  allreduce_fn fn;
+  void *ctx;
+  size_t v_row0;
+};
+
 static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds,
                            double *dV, size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const RowShard *rs = nullptr) {
   const size_t mn = std::min(m, n);
   int variant = o.variant;
   if (variant == SVDJ_VARIANT_AUTO) {
@@ -249,7 +257,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   }
 
   if (rotate_v) {
-    if (int rc = launch_set_identity(dV, ldv, vrows, n, stream)) return rc;
+    if (int rc = launch_set_identity(dV, ldv, vrows, n, stream, rs ? rs->v_row0 : 0)) return rc;
     st.launches += 1;
   }
 
@@ -369,6 +377,11 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (o.threshold_mode == SVDJ_THRESH_REL) {
     if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
     if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+    if (rs) {  // global column norms: sum of the ranks' squares
+      if (int rc = launch_square(d_norms.as<double>(), n, stream)) return rc;
+      if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) return SVDJ_ERR_CUDA;
+      if (int rc = launch_sqrt(d_norms.as<double>(), n, stream)) return rc;
+    }
     std::vector<double> hn(n);
     SVDJ_CUDA_TRY(cudaMemcpyAsync(hn.data(), d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
     SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
@@ -377,6 +390,21 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     const double fl = o.tol * mx;
     a.floor2 = b.floor2 = fl * fl;
     st.launches += 1;
+  }
+
+  RowHook row_hook;
+  DevBuf d_gred;
+  if (rs) {
+    if (!(block && wide)) {
+      set_error("row-sharded solve: needs the 64-column block path (n >= 128, 16-byte aligned columns, even ld)");
+      return SVDJ_ERR_UNSUPPORTED;
+    }
+    const size_t gd = blk32_gred_doubles(n + 256);
+    if (int rc = d_gred.alloc(sizeof(double) * gd)) return rc;
+    SVDJ_CUDA_TRY(cudaMemsetAsync(d_gred.p, 0, sizeof(double) * gd, stream));
+    row_hook.fn = rs->fn;
+    row_hook.ctx = rs->ctx;
+    row_hook.gred = d_gred.as<double>();
   }
 
   SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, stream));
@@ -395,8 +423,13 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
           probes[probes_used].active_pairs = d_probe.as<unsigned long long>();
           probe = &probes[probes_used++];
         }
-        if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, d_gpart.as<double>(), d_w.as<double>(),
-                                                                  d_wflag.as<int>(), stream, &step_launches, probe))
+        if (rs) {
+          if (int rc = blk32_launch_step(b, k, d_gpart.as<double>(), d_w.as<double>(), d_wflag.as<int>(), stream,
+                                         &step_launches, probe, &row_hook))
+            return rc;
+        } else if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, d_gpart.as<double>(), d_w.as<double>(),
+                                                                         d_wflag.as<int>(), stream, &step_launches, probe,
+                                                                         nullptr))
           return rc;
       } else {
         if (int rc = l1_launch_step(a, k, d_scratch.as<double>(), stream, &step_launches)) return rc;
@@ -448,6 +481,11 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
   }
   if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+  if (rs) {  // sigma_k^2 = sum over the ranks of the squared norms of their rows of column k
+    if (int rc = launch_square(d_norms.as<double>(), n, stream)) return rc;
+    if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) return SVDJ_ERR_CUDA;
+    if (int rc = launch_sqrt(d_norms.as<double>(), n, stream)) return rc;
+  }
   st.launches += 1;
   const bool scale_u = (jobu == SVDJ_ALLVEC || jobu == SVDJ_SOMEVEC);
 
@@ -475,10 +513,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
                                     cudaMemcpyDeviceToDevice, stream));
     st.launches += 1;
     if (rotate_v) {
-      if (int rc = launch_gather_columns(dV, ldv, d_tmp.as<double>(), n, n, n, d_perm.as<unsigned>(), nullptr, 0,
-                                         stream))
+      const size_t vr = rs ? vrows : n;  // rows of V held here
+      if (int rc = launch_gather_columns(dV, ldv, d_tmp.as<double>(), vr, vr, n, d_perm.as<unsigned>(), nullptr, 0, stream))
         return rc;
-      SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dV, ldv * sizeof(double), d_tmp.p, n * sizeof(double), n * sizeof(double), n,
+      SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dV, ldv * sizeof(double), d_tmp.p, vr * sizeof(double), vr * sizeof(double), n,
                                       cudaMemcpyDeviceToDevice, stream));
       st.launches += 1;
     }
@@ -564,6 +602,41 @@ size_t svdj_block_schedule_step(size_t nb, int vranks, size_t step, size_t *pq) 
     pq[2 * i + 1] = pr.q;
   }
   return pairs;
+}
+
+int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double *dA, size_t lda, double *ds,
+                            double *dV, size_t ldv, size_t vrows_local, size_t v_row0, const svdj_opts *opts,
+                            svdj_stats *stats, void *stream, svdj_allreduce_fn allreduce, void *ctx) {
+  g_error[0] = 0;
+  svdj_stats local;
+  svdj_stats &st = stats ? *stats : local;
+  std::memset(&st, 0, sizeof(st));
+  if (m_local == 0 || m_local > 0x7fffffffu) return -3;
+  if (n < 128 || n > 0x7fffffffu) return -4;
+  if (dA == nullptr) return -5;
+  if (lda < m_local) return -6;
+  if (ds == nullptr) return -7;
+  const bool want_v = (jobv == SVDJ_ALLVEC || jobv == SVDJ_SOMEVEC);
+  if (want_v && dV == nullptr) return -8;
+  if (want_v && ldv < vrows_local) return -9;
+  if (want_v && (vrows_local == 0 || v_row0 + vrows_local > n)) return -10;
+  if (opts == nullptr || !(opts->tol > 0.0)) {
+    set_error("svdj_dgesvd_rows_device: opts->tol must be set (the relative threshold uses the global row count)");
+    return -12;
+  }
+  if (allreduce == nullptr) return -15;
+  const double t0 = now_s();
+  svdj_opts o = resolve_opts(opts, m_local);
+  o.variant = SVDJ_VARIANT_BLOCK;
+  o.block = 32;
+  o.threshold_mode = SVDJ_THRESH_REL;
+  DeviceGuard guard;
+  if (int rc = guard.enter(o.device)) return rc;
+  RowShard rs{allreduce, ctx, v_row0};
+  const int rc = solve_on_device(jobu, jobv, m_local, n, dA, lda, ds, dV, ldv, want_v ? vrows_local : 0, o, st,
+                               static_cast<cudaStream_t>(stream), &rs);
+  st.seconds_total = now_s() - t0;
+  return rc;
 }
 
 size_t svdj_step_scratch_doubles(size_t m, size_t n) { return l1_scratch_doubles(m, n); }

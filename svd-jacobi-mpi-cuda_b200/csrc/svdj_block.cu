@@ -677,7 +677,8 @@ void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doub
 }
 
 int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                    unsigned long long *launches, const BlockProbe *probe) {
+                    unsigned long long *launches, const BlockProbe *probe, const RowHook *rows) {
+  if (rows != nullptr) return SVDJ_ERR_UNSUPPORTED;  // the row-sharded driver uses the 64-column kernels
   const unsigned pairs = a_in.nb / 2;
   if (pairs == 0) return SVDJ_OK;
   BlockArgs a = a_in;

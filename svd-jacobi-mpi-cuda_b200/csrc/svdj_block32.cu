@@ -672,6 +672,20 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
   cp_async_wait<0>();
 }
 
+// Sum of the row splits' partial Gram matrices (row-sharded driver: what goes into the all-reduce over the ranks)
+__global__ void __launch_bounds__(256) blk32_gram_reduce_kernel(const double *__restrict__ gpart, const unsigned splits,
+                                                                const unsigned count, double *__restrict__ gred) {
+  griddep_launch();
+  griddep_wait();
+  const unsigned pair = blockIdx.x;
+  const double *src = gpart + (size_t)pair * splits * kGramPart32;
+  for (unsigned i = threadIdx.x; i < count; i += 256) {
+    double s = 0.0;
+    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+    gred[(size_t)pair * kGramPart32 + i] = s;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -716,8 +730,10 @@ bool blk32_supported(const BlockArgs &a) {
   return aligned && aligned2 && (a.nb / 2) <= (unsigned)kMaxPairs32 && a.nb >= 2;
 }
 
+size_t blk32_gred_doubles(size_t n) { return (size_t)(blk32_num_blocks(n) / 2 + 8) * kGramPart32; }
+
 int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                      unsigned long long *launches, const BlockProbe *probe) {
+                      unsigned long long *launches, const BlockProbe *probe, const RowHook *rows) {
   const unsigned pairs = a_in.nb / 2;
   if (pairs == 0) return SVDJ_OK;
   BlockArgs a = a_in;
@@ -778,8 +794,21 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   else
     SVDJ_CUDA_TRY(launch_k(blk32_gram_kernel<false>, dim3(pairs, splits), 128, sizeof(double) * kG32Stages * kG32TileDoubles, st, a, k, rps, gpart));
   if (probe && probe_kernel == 1) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
+  const double *gsrc = gpart;
+  unsigned gsplits = splits;
+  if (rows != nullptr) {  // row-sharded: this rank's rows only so far; sum over the splits, then over the ranks
+    const unsigned count = (a.gram_mode == 2) ? 16u * 64u : (unsigned)kGramPart32;
+    SVDJ_CUDA_TRY(launch_k(blk32_gram_reduce_kernel, dim3(pairs), 256, 0, st, (const double *)gpart, splits, count, rows->gred));
+    if (int rc = rows->fn(rows->ctx, rows->gred, (size_t)pairs * kGramPart32, st)) {
+      set_error("row-sharded step: the caller's all-reduce returned %d", rc);
+      return SVDJ_ERR_CUDA;
+    }
+    if (launches) *launches += 1;
+    gsrc = rows->gred;
+    gsplits = 1;
+  }
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  SVDJ_CUDA_TRY(launch_k(blk32_eig_kernel, dim3(pairs), 1024, kE32Smem, st, a, k, splits, gpart, wbuf, wflag));
+  SVDJ_CUDA_TRY(launch_k(blk32_eig_kernel, dim3(pairs), 1024, kE32Smem, st, a, k, gsplits, gsrc, wbuf, wflag));
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   SVDJ_CUDA_TRY(launch_k(blk32_update_kernel, dim3(sm_count * kU32CtasPerSm), kU32Threads, kU32Smem, st, a, k, wbuf, wflag, pairs,

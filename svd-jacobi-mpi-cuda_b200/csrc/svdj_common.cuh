@@ -267,6 +267,17 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, unsigned block, s
   return cudaLaunchKernelEx(&c, kern, std::forward<Args>(args)...);
 }
 
+// Row-sharded driver: every rank holds a slice of the rows of A and V and all the columns.  The Gram matrices of a
+// step are the only quantity that needs the other ranks: after K1 the per-pair partial sums are reduced over the
+// row splits into `gred` and summed over the ranks by the caller's all-reduce (in place, on the stream); every
+// rank then runs the same eigen-solves and updates its own rows.
+typedef int (*allreduce_fn)(void *ctx, double *dptr, size_t count, void *stream);
+struct RowHook {
+  allreduce_fn fn = nullptr;
+  void *ctx = nullptr;
+  double *gred = nullptr;  // pairs x kGramPart32 doubles
+};
+
 struct BlockProbe {
   cudaEvent_t before = nullptr, after = nullptr;
   unsigned long long *active_pairs = nullptr;
@@ -274,18 +285,22 @@ struct BlockProbe {
 unsigned blk_num_blocks(size_t n);
 void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
 // k = 1-based step of the round-robin ordering over the nb blocks
+struct RowHook;
 int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                    unsigned long long *launches, const BlockProbe *probe = nullptr);
+                    unsigned long long *launches, const BlockProbe *probe = nullptr, const RowHook *rows = nullptr);
 
 // The same step with column blocks of 32 (svdj_block32.cu); single buffer, aligned layouts only.
 unsigned blk32_num_blocks(size_t n);
 void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
 bool blk32_supported(const BlockArgs &a);
 int blk32_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
-                      unsigned long long *launches, const BlockProbe *probe = nullptr);
+                      unsigned long long *launches, const BlockProbe *probe = nullptr, const RowHook *rows = nullptr);
+size_t blk32_gred_doubles(size_t n);
 
 // Finalisation (svdj_finalize.cu)
-int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st);
+int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0 = 0);
+int launch_square(double *x, size_t n, cudaStream_t st);
+int launch_sqrt(double *x, size_t n, cudaStream_t st);
 int launch_column_norms(const double *A, size_t lda, size_t m, size_t n, double *norms, cudaStream_t st);
 // out[:, k] = in[:, perm[k]] * (scale ? 1/sigma[k] : 1); columns k >= ncols_scaled copied unscaled
 int launch_gather_columns(const double *in, size_t ldin, double *out, size_t ldout, size_t rows, size_t ncols,

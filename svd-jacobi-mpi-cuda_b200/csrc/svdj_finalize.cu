@@ -5,10 +5,20 @@
 
 namespace svdj {
 
-__global__ void set_identity_kernel(double *__restrict__ V, size_t ldv, unsigned rows) {
+// rows row0 .. row0 + rows - 1 of the identity (row0 != 0: a rank of the row-sharded driver holds a slice of V)
+__global__ void set_identity_kernel(double *__restrict__ V, size_t ldv, unsigned rows, unsigned row0) {
   const unsigned col = blockIdx.x;
   double *c = V + (size_t)col * ldv;
-  for (unsigned i = threadIdx.x; i < rows; i += blockDim.x) c[i] = (i == col) ? 1.0 : 0.0;
+  for (unsigned i = threadIdx.x; i < rows; i += blockDim.x) c[i] = (row0 + i == col) ? 1.0 : 0.0;
+}
+
+__global__ void square_kernel(double *__restrict__ x, unsigned n) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = x[i] * x[i];
+}
+__global__ void sqrt_kernel(double *__restrict__ x, unsigned n) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = sqrt(x[i]);
 }
 
 __global__ void __launch_bounds__(256) column_norms_kernel(const double *__restrict__ A, size_t lda, unsigned m,
@@ -45,9 +55,22 @@ __global__ void gather_columns_kernel(const double *__restrict__ in, size_t ldin
   }
 }
 
-int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st) {
+int launch_square(double *x, size_t n, cudaStream_t st) {
   if (n == 0) return SVDJ_OK;
-  set_identity_kernel<<<(unsigned)n, 256, 0, st>>>(V, ldv, (unsigned)rows);
+  square_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, (unsigned)n);
+  SVDJ_CUDA_TRY(cudaGetLastError());
+  return SVDJ_OK;
+}
+int launch_sqrt(double *x, size_t n, cudaStream_t st) {
+  if (n == 0) return SVDJ_OK;
+  sqrt_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, (unsigned)n);
+  SVDJ_CUDA_TRY(cudaGetLastError());
+  return SVDJ_OK;
+}
+
+int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0) {
+  if (n == 0) return SVDJ_OK;
+  set_identity_kernel<<<(unsigned)n, 256, 0, st>>>(V, ldv, (unsigned)rows, (unsigned)row0);
   SVDJ_CUDA_TRY(cudaGetLastError());
   return SVDJ_OK;
 }

@@ -133,7 +133,7 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
       b.V2_st = dstV_right ? dstV_right : dV_right;
       b.force_update = 1;
     }
-    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr)) return rc;
+    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr, nullptr)) return rc;
   }
   return SVDJ_OK;
 }

@@ -191,3 +191,21 @@ def test_quadratic_stop_rule():
     assert not ring.quadratic_stop(2153, 1.8e-7, 20000 * 2.0 ** -53)  # 7e-11 > tol / 2
     assert not ring.quadratic_stop(10, 0.0, tol)            # a backend that does not track the cosine never stops early
     assert not ring.quadratic_stop(1, 2e-6, 1.0)            # the cosine itself must be small
+
+
+def test_row_partition_tiles_the_rows():
+    """Row-sharded driver: contiguous slices that tile [0, m), whole 64-row tiles except the last, near even."""
+    from importlib import import_module
+    rows = import_module("svd-jacobi-mpi-cuda_b200.rows")
+    for m, parts, mult in [(1048576, 8, 64), (1000, 3, 64), (512, 8, 1), (100, 8, 64), (65, 2, 64), (4096, 1, 64)]:
+        p = rows.row_partition(m, parts, mult)
+        assert len(p) == parts and p[0][0] == 0
+        assert all(cnt > 0 for _, cnt in p)
+        assert all(p[i][0] + p[i][1] == p[i + 1][0] for i in range(parts - 1))
+        assert p[-1][0] + p[-1][1] == m
+        if m >= parts * mult * 2:
+            assert all(cnt % mult == 0 for _, cnt in p[:-1])
+            assert max(c for _, c in p) - min(c for _, c in p) <= 2 * mult
+    import pytest
+    with pytest.raises(ValueError):
+        rows.row_partition(3, 4)
