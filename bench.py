@@ -366,6 +366,7 @@ def run_rows(args, svdj, world, rank, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     per_step_s = float(t.item()) / args.steps
     st = stats[-1]
+    ar_calls, ar_bytes = solver.allreduce_calls / args.steps, solver.allreduce_bytes / args.steps
 
     # e2e: every rank's rows start in its own pinned host memory and its rows of U and V (and sigma) end there
     hA = A_rows.cpu().pin_memory()
@@ -417,8 +418,7 @@ def run_rows(args, svdj, world, rank, local_rank):
                        "parallelism": f"rows sharded over {world} GPU(s): {ml} rows of A and {solver.v_local} rows of V "
                                       "per rank, one all-reduce of the block pairs' Gram matrices per step"},
             "sweeps": st.sweeps, "rotations_applied": int(st.applied),
-            "rows": {"allreduce_calls_per_solve": solver.allreduce_calls / args.steps,
-                     "allreduce_bytes_per_solve": solver.allreduce_bytes / args.steps},
+            "rows": {"allreduce_calls_per_solve": ar_calls, "allreduce_bytes_per_solve": ar_bytes},
             "roofline": {"bound": "tensor", "achieved": tfs, "peak": 36.9, "unit": "TFLOP/s", "frac": tfs / 36.9,
                          "traffic": None, "kernel": "blk32_update_kernel on rank 0's rows",
                          "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md",
