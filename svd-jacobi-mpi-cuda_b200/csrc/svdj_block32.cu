@@ -503,12 +503,13 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3: X <- X W, Y <- Y W for the 64-column panels.  One persistent CTA of 16 warps per SM walks the flat list
-// of 128-row x 64-column tiles of the block pairs that rotated; tiles arrive through a 2-stage cp.async
-// pipeline (1 KiB contiguous per pair of warps); W (64 x 64) sits in shared memory and feeds the DMMA
-// B-fragments.  Warp w owns rows 16 (w & 7) .. +15 of the tile and output columns 32 (w >> 3) .. +31: each
-// B-fragment serves the two 8-row halves, and 16 warps per SM keep the FP64 tensor pipe fed (with 8 warps
-// the same kernel ran at 42 % of the DMMA issue peak: the pipe needs ~4 warps per scheduler).
+// K3: X <- X W, Y <- Y W for the 64-column panels.  Two persistent CTAs of 8 warps per SM walk the flat list of
+// 64-row x 64-column tiles of the block pairs that rotated; tiles arrive through a 2-stage cp.async pipeline
+// (512 contiguous bytes per warp-level copy); W (64 x 64) sits in shared memory in fragment order and feeds the
+// DMMA B-fragments.  Warp w owns rows 16 (w & 3) .. +15 of the tile and output columns 32 (w >> 2) .. +31: each
+// B-fragment serves the two 8-row halves.  What bounds it (0.67-0.74 of the DMMA peak): profiles/r1_k3_inner.md --
+// the loop itself runs at the peak from shared memory; the tile loads and the result stores each cost ~15 % on the
+// SM side, and a launch of this size pays ~15 us of ramp and tail.
 // ------------------------------------------------------------------------------------------------
 static constexpr int kU32Rows = 64;
 static constexpr int kU32Stride = kU32Rows + 4;
