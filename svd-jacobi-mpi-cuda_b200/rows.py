@@ -46,8 +46,27 @@ def row_partition(m: int, parts: int, multiple: int = 64) -> list[tuple[int, int
     return out
 
 
+class LibBackend:
+    """The product path: libsvdj's row-sharded entry point on this rank's GPU (there is no CPU fallback)."""
+
+    def solve(self, solver: "RowShardSolver", allow_not_converged: bool) -> Stats:
+        st = Stats()
+        opts = default_opts(tol=solver.tol, max_sweeps=solver.max_sweeps)
+        stream = torch.cuda.current_stream(solver.device).cuda_stream
+        with torch.cuda.device(solver.device):
+            rc = lib.svdj_dgesvd_rows_device(AllVec, AllVec, solver.m_local, solver.n, solver.A.data_ptr(), solver.lda,
+                                             solver.sigma.data_ptr(), solver.V.data_ptr(), solver.ldv, solver.v_local,
+                                             solver.v_row0, C.byref(opts), C.byref(st), C.c_void_p(stream),
+                                             solver._cb, None)
+        st.rc = rc
+        if rc < 0 or rc > 1 or (rc == 1 and not allow_not_converged):
+            raise RuntimeError(f"svdj_dgesvd_rows_device -> {rc}: {lib.svdj_last_error().decode()}")
+        return st
+
+
 class RowShardSolver:
-    def __init__(self, m: int, n: int, device, group=None, tol: Optional[float] = None, max_sweeps: int = 60):
+    def __init__(self, m: int, n: int, device, group=None, tol: Optional[float] = None, max_sweeps: int = 60,
+                 backend=None):
         self.m, self.n, self.device, self.group = m, n, torch.device(device), group
         self.P = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -63,15 +82,19 @@ class RowShardSolver:
         self.allreduce_calls = 0
         self.allreduce_bytes = 0
         self._cb = AllreduceFn(self._allreduce)             # keep the trampoline alive
+        self.backend = backend if backend is not None else LibBackend()   # tests pass a numpy stand-in (gloo)
+
+    def allreduce_tensor(self, t: torch.Tensor) -> None:
+        """Sum over the ranks, in place (on torch's current stream for CUDA tensors = the solve's stream)."""
+        if self.P > 1:
+            dist.all_reduce(t, group=self.group)
+        self.allreduce_calls += 1
+        self.allreduce_bytes += t.numel() * t.element_size()
 
     # called by libsvdj between the Gram kernel and the eigen-solves of every step (and for the column norms)
     def _allreduce(self, ctx, dptr, count, stream) -> int:
         try:
-            if self.P > 1:
-                t = torch.as_tensor(_DeviceMemory(int(dptr), int(count)), device=self.device)
-                dist.all_reduce(t, group=self.group)         # on torch's current stream = the solve's stream
-            self.allreduce_calls += 1
-            self.allreduce_bytes += 8 * int(count)
+            self.allreduce_tensor(torch.as_tensor(_DeviceMemory(int(dptr), int(count)), device=self.device))
             return 0
         except Exception:                                    # never let an exception cross the C frame
             import traceback
@@ -85,18 +108,8 @@ class RowShardSolver:
         self.A.zero_()
         self.A[:, : self.m_local].copy_(A_rows)
 
-    def solve(self, allow_not_converged: bool = False) -> Stats:
-        st = Stats()
-        opts = default_opts(tol=self.tol, max_sweeps=self.max_sweeps)
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        with torch.cuda.device(self.device):
-            rc = lib.svdj_dgesvd_rows_device(AllVec, AllVec, self.m_local, self.n, self.A.data_ptr(), self.lda,
-                                             self.sigma.data_ptr(), self.V.data_ptr(), self.ldv, self.v_local,
-                                             self.v_row0, C.byref(opts), C.byref(st), C.c_void_p(stream), self._cb, None)
-        st.rc = rc
-        if rc < 0 or rc > 1 or (rc == 1 and not allow_not_converged):
-            raise RuntimeError(f"svdj_dgesvd_rows_device -> {rc}: {lib.svdj_last_error().decode()}")
-        return st
+    def solve(self, allow_not_converged: bool = False):
+        return self.backend.solve(self, allow_not_converged)
 
     @property
     def U_local(self) -> torch.Tensor:

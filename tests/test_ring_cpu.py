@@ -209,3 +209,96 @@ def test_row_partition_tiles_the_rows():
     import pytest
     with pytest.raises(ValueError):
         rows.row_partition(3, 4)
+
+
+class NumpyRowsBackend:
+    """Stand-in for rows.LibBackend: the same protocol in numpy at column-pair granularity -- per step the partial
+    (alpha, beta, gamma) of every pair of the reference's schedule are summed over the ranks with the solver's
+    all-reduce, every rank derives the same rotations and applies them to its own rows of A and V."""
+
+    def solve(self, solver, allow_not_converged):
+        n, ml, vl = solver.n, solver.m_local, solver.v_local
+        A = solver.A.numpy()[:, :ml]          # row j = column j, this rank's rows
+        V = solver.V.numpy()[:, :vl]
+        V[:] = 0.0
+        V[solver.v_row0 + np.arange(vl), np.arange(vl)] = 1.0      # rows v_row0.. of the identity
+        steps = H.oracle_lib().oracle_num_steps(n)
+        sweeps, converged = 0, False
+        for sweep in range(solver.max_sweeps):
+            applied = 0
+            for st in range(steps):
+                pairs = H.oracle_schedule(n, st)
+                pairs = pairs[(pairs[:, 0] < n) & (pairs[:, 1] < n)]
+                trip = torch.from_numpy(np.stack([np.einsum("ij,ij->i", A[pairs[:, 0]], A[pairs[:, 1]]),
+                                                  np.einsum("ij,ij->i", A[pairs[:, 0]], A[pairs[:, 0]]),
+                                                  np.einsum("ij,ij->i", A[pairs[:, 1]], A[pairs[:, 1]])], axis=1))
+                solver.allreduce_tensor(trip)
+                for (p, q), (al, be, ga) in zip(pairs.tolist(), trip.numpy().tolist()):
+                    if not abs(al) > solver.tol * np.sqrt(be * ga):
+                        continue
+                    tau = (ga - be) / (2.0 * al)
+                    t = 1.0 / (tau + np.sqrt(1 + tau * tau)) if tau >= 0 else 1.0 / (tau - np.sqrt(1 + tau * tau))
+                    c = 1.0 / np.sqrt(1 + t * t)
+                    s = t * c
+                    for X in (A, V):
+                        xp, xq = X[p].copy(), X[q].copy()
+                        X[p], X[q] = c * xp - s * xq, s * xp + c * xq
+                    applied += 1
+            sweeps += 1
+            if applied == 0:
+                converged = True
+                break
+        sq = torch.from_numpy(np.einsum("ij,ij->i", A, A))
+        solver.allreduce_tensor(sq)
+        sigma = np.sqrt(sq.numpy())
+        order = np.argsort(-sigma, kind="stable")
+        A[:] = A[order] / sigma[order][:, None]
+        V[:] = V[order]
+        solver.sigma.copy_(torch.from_numpy(sigma[order].copy()))
+        return {"sweeps": sweeps, "converged": converged}
+
+
+def _rows_worker(rank, world, port, m, n, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from importlib import import_module
+        rows = import_module("svd-jacobi-mpi-cuda_b200.rows")
+        solver = rows.RowShardSolver(m, n, torch.device("cpu"), backend=NumpyRowsBackend())
+        parts = rows.row_partition(m, world)
+        assert (solver.row0, solver.m_local) == parts[rank]
+        assert (solver.v_row0, solver.v_local) == rows.row_partition(n, world, 1)[rank]
+        A0 = H.normal_matrix(m, n, seed=m * 3 + n)
+        solver.fill_local(torch.from_numpy(np.ascontiguousarray(A0[solver.row0:solver.row0 + solver.m_local].T)))
+        st = solver.solve()
+        assert st["converged"]
+        # one all-reduce per step of every sweep, one for sigma
+        steps = H.oracle_lib().oracle_num_steps(n)
+        assert solver.allreduce_calls == st["sweeps"] * steps + 1
+        np.savez(f"{out_path}.{rank}.npz", U=solver.U_local.numpy().T, V=solver.V_local.numpy().T,
+                 s=solver.sigma.numpy(), sweeps=st["sweeps"])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,m,n", [(2, 300, 24), (3, 500, 20)])
+def test_row_sharded_protocol_with_gloo(tmp_path, world, m, n):
+    """The row-sharded driver's host side (partition, buffers, all-reduce plumbing, row slices of U and V) with a
+    numpy stand-in for the per-rank compute: every rank ends with the same sigma, the stacked slices are an SVD."""
+    out = str(tmp_path / "rows")
+    mp.spawn(_rows_worker, args=(world, _free_port(), m, n, out), nprocs=world, join=True)
+    parts = [np.load(f"{out}.{r}.npz") for r in range(world)]
+    for p in parts[1:]:
+        assert np.array_equal(p["s"], parts[0]["s"]) and int(p["sweeps"]) == int(parts[0]["sweeps"])
+    U = np.concatenate([p["U"] for p in parts], axis=0)
+    V = np.concatenate([p["V"] for p in parts], axis=0)
+    A0 = H.normal_matrix(m, n, seed=m * 3 + n)
+    s = parts[0]["s"]
+    assert U.shape == (m, n) and V.shape == (n, n)
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    q = H.svd_quality(A0, U, s, V)
+    bound = 10 * max(m, n) * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+    Uo, so, Vo, ost, rc = H.oracle_svd(A0)                  # same sweeps as the single-process oracle
+    assert int(parts[0]["sweeps"]) == ost.sweeps
