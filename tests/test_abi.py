@@ -126,3 +126,28 @@ def test_no_cpu_fallback_without_a_device(svdj):
     with pytest.raises(svdj.SvdjError) as e:
         svdj.dgesvd(0, 0, 4, 4, A, 4, np.zeros(4), np.zeros((4, 4), order="F"), 4)
     assert e.value.code in (svdj.ERR_CUDA, svdj.ERR_ALLOC)
+
+
+def test_rows_entry_point_arguments_and_no_fallback(svdj):
+    """svdj_dgesvd_rows_device: bad arguments come back as negative argument numbers before anything touches the
+    device; with valid arguments and no GPU it fails with a CUDA error -- it never computes on the host."""
+    import ctypes as C
+    import torch
+    cb = svdj.AllreduceFn(lambda ctx, ptr, count, stream: 0)
+    st = svdj.Stats()
+    p = lambda v: C.c_void_p(v)   # never dereferenced on the host
+
+    def call(m_local, n, vrows, v_row0, opts, fn=cb):
+        return svdj.lib.svdj_dgesvd_rows_device(svdj.AllVec, svdj.AllVec, m_local, n, p(0x1000), max(m_local, 1), p(0x2000),
+                                                p(0x3000), max(vrows, 1), vrows, v_row0, C.byref(opts), C.byref(st), None,
+                                                fn, None)
+
+    with_tol = svdj.default_opts(tol=1e-12)
+    assert call(0, 256, 256, 0, with_tol) == -3                     # no rows
+    assert call(1000, 64, 64, 0, with_tol) == -4                    # n < 128: no 64-column block pairs
+    assert call(1000, 256, 200, 100, with_tol) == -10               # V rows 100..299 of a 256-row V
+    assert call(1000, 256, 256, 0, svdj.default_opts()) == -12      # tol must be set: the local m is not the global one
+    assert b"tol" in svdj.lib.svdj_last_error()
+    assert call(1000, 256, 256, 0, with_tol, svdj.AllreduceFn(0)) == -15   # no all-reduce
+    if not torch.cuda.is_available():
+        assert call(1000, 256, 256, 0, with_tol) in (svdj.ERR_CUDA, svdj.ERR_ALLOC)
