@@ -335,6 +335,9 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   // Tall inputs (m >= 8 n): the eigen-solve does not grow with m while K1/K3 do, so extra inner sweeps are free
   // and every outer sweep saved counts (1,048,576 x 512: 12 sweeps with one inner sweep, 8 with three).
   b.max_inner_sweeps = (m >= 8 * n) ? 3 : (n >= 8192) ? 2 : 1;
+  // row-sharded: every rank must take the same decisions (they all run the same eigen-solves on the same Gram
+  // matrices); the local row count differs between ranks, so nothing may depend on it -- tall by definition
+  if (rs) b.max_inner_sweeps = 3;
   if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) {
     const int v = std::atoi(env);
     if (v > 0) b.max_inner_sweeps = v;
