@@ -59,14 +59,17 @@ enum {
 };
 
 typedef struct svdj_opts {
-  double tol;         /* <= 0: default m * 2^-53 (LAPACK dgesvj's choice) in REL mode, 1e-16 in ABS mode */
+  double tol;         /* <= 0: default.  REL mode: LAPACK dgesvj's choice -- sqrt(m) * 2^-53 when U or V is wanted (the
+                         columns then come out orthogonal to 10 n eps), m * 2^-53 for NoVec/NoVec.  ABS mode: 1e-16 */
   int max_sweeps;     /* <= 0: default 60.  The reference runs exactly 1 (lib/JacobiMethods.cu:234) */
   int sort_desc;      /* 1: sigma descending, U/V columns permuted alike (default); 0: reference's raw column order */
   int variant;        /* SVDJ_VARIANT_* */
   int threshold_mode; /* SVDJ_THRESH_* */
   int block;          /* column-block width of SVDJ_VARIANT_BLOCK: 16 or 32; 0 = library decides (32 from n = 4096) */
   int device;         /* CUDA device ordinal; < 0 = the calling thread's current device */
-  int use_graph;      /* 1: replay each sweep from a CUDA graph; 0: plain launches; < 0: library decides */
+  int precondition;   /* QR front-end before the sweeps (m >= n >= 64): 0 none; 1: de Rijk column sort, A P = Q R by
+                         blocked Householder, Jacobi on R^T; 2: R^T factored once more (strongly graded spectra);
+                         < 0: the library decides (default).  All on the device, this library's own kernels */
 } svdj_opts;
 
 typedef struct svdj_stats {
@@ -87,6 +90,9 @@ typedef struct svdj_stats {
                                     step, or the block path's update kernel (probed with events every 8th step) */
   unsigned long long step_kernel_launches; /* launches of that kernel (block path: the probed ones) */
   unsigned long long probe_block_pairs;    /* block path: block pairs updated by the probed launches */
+  double seconds_precond;        /* device time of the QR front-end and of applying Q afterwards (0 without it) */
+  int precondition;              /* QR steps that ran (0, 1 or 2) */
+  int reserved1;
 } svdj_stats;
 
 /* Fills *opts with the defaults described above. */
@@ -175,6 +181,11 @@ int svdj_step_device_noalloc(size_t m, size_t n, double *dA, size_t lda, double 
 enum { SVDJ_PHASE_ALL = 0, SVDJ_PHASE_CROSS = 1 };
 int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out);
 int svdj_ring_ws_destroy(void *ws);
+/* Columns whose norm is <= floor_norm are numerically zero and are never rotated (rank-deficient and m < n
+ * inputs: without it their noise keeps every sweep rotating).  The driver passes tol * (largest column norm of the
+ * whole input), the same floor the single-GPU solver uses; 0 (the default) switches it off.  The reference has no
+ * such guard (it runs one sweep whatever happens, main.cu:482). */
+int svdj_ring_ws_set_floor(void *ws, double floor_norm);
 int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right,
                            size_t lda, double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase,
                            double tol, int inner_sweeps, unsigned long long *d_counters, void *stream);
@@ -209,7 +220,7 @@ int svdj_ipc_close(void *peer_ptr);
  * of its block pairs: `allreduce(ctx, dptr, count, stream)` must sum `count` doubles at device pointer `dptr` over
  * all ranks, in place, ordered on `stream` (e.g. ncclAllReduce / torch.distributed.all_reduce), and return 0.
  * Every rank then runs the same eigen-solves and updates its own rows; sigma comes out complete on every rank, U
- * and V as the caller's row slices.  opts->tol must be set (m_global * 2^-53 for the library default).  n >= 128,
+ * and V as the caller's row slices.  opts->tol must be set (sqrt(m_global) * 2^-53 for the library default).  n >= 128,
  * 16-byte aligned columns and even leading dimensions are required (SVDJ_ERR_UNSUPPORTED otherwise).
  * Replaces, for m >> n, the reference's distribution of a step's pairs over MPI ranks through rank 0
  * (main.cu:583-942): there every rank needs whole columns of m doubles per pair, here 18 KiB per block pair. */
@@ -217,6 +228,21 @@ typedef int (*svdj_allreduce_fn)(void *ctx, double *dptr, size_t count, void *st
 int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double *dA, size_t lda, double *ds,
                             double *dV, size_t ldv, size_t vrows_local, size_t v_row0, const svdj_opts *opts,
                             svdj_stats *stats, void *stream, svdj_allreduce_fn allreduce, void *ctx);
+
+/*
+ * The QR front-end's building blocks on device buffers (what svdj_opts.precondition runs before and after the
+ * sweeps).  The reference has no factorisation step: its doc block names tall inputs as the use-case
+ * (lib/JacobiMethods.cu:12-14) and then sweeps the raw columns (main.cu:478-1384).
+ * svdj_qr_factor_device: blocked Householder QR of Y (m x n, m >= n, column-major, ld >= m) in place, LAPACK dgeqrf's
+ *   storage: R on and above the diagonal, the Householder vectors below it (unit diagonal implied); dT receives one
+ *   32 x 32 upper-triangular factor per panel of 32 columns, svdj_qr_tfactor_doubles(n) doubles in all
+ *   (H_1 .. H_32 = I - V T V^T).  m <= 65536.
+ * svdj_qr_apply_q_device: C (m x ncols, ldc >= m) <- Q C with the Q of a previous svdj_qr_factor_device.
+ */
+size_t svdj_qr_tfactor_doubles(size_t n);
+int svdj_qr_factor_device(size_t m, size_t n, double *dY, size_t ld, double *dT, void *stream);
+int svdj_qr_apply_q_device(size_t m, size_t n, const double *dY, size_t ld, const double *dT, double *dC, size_t ldc,
+                           size_t ncols, void *stream);
 
 /* Number of steps of one sweep for n columns: 2*((n+1)/2) - 1 (main.cu:478, 498, 943). */
 size_t svdj_num_steps(size_t n);

@@ -48,7 +48,7 @@ class Opts(C.Structure):
         ("threshold_mode", C.c_int),
         ("block", C.c_int),
         ("device", C.c_int),
-        ("use_graph", C.c_int),
+        ("precondition", C.c_int),
     ]
 
 
@@ -70,6 +70,9 @@ class Stats(C.Structure):
         ("step_kernel_ms", C.c_double),
         ("step_kernel_launches", C.c_ulonglong),
         ("probe_block_pairs", C.c_ulonglong),
+        ("seconds_precond", C.c_double),
+        ("precondition", C.c_int),
+        ("reserved1", C.c_int),
     ]
 
     def as_dict(self) -> dict:
@@ -86,6 +89,10 @@ EXPORTS = (
     "svdj_step_device_noalloc",
     "svdj_ring_ws_create",
     "svdj_ring_ws_destroy",
+    "svdj_ring_ws_set_floor",
+    "svdj_qr_tfactor_doubles",
+    "svdj_qr_factor_device",
+    "svdj_qr_apply_q_device",
     "svdj_ring_phase_device",
     "svdj_ring_finalize_device",
     "svdj_ring_phase_send_device",
@@ -126,6 +133,14 @@ def _load() -> C.CDLL:
     lib.svdj_ring_ws_create.restype = i
     lib.svdj_ring_ws_destroy.argtypes = [vp]
     lib.svdj_ring_ws_destroy.restype = i
+    lib.svdj_ring_ws_set_floor.argtypes = [vp, dbl]
+    lib.svdj_ring_ws_set_floor.restype = i
+    lib.svdj_qr_tfactor_doubles.argtypes = [sz]
+    lib.svdj_qr_tfactor_doubles.restype = sz
+    lib.svdj_qr_factor_device.argtypes = [sz, sz, vp, sz, vp, vp]
+    lib.svdj_qr_factor_device.restype = i
+    lib.svdj_qr_apply_q_device.argtypes = [sz, sz, vp, sz, vp, vp, sz, sz, vp]
+    lib.svdj_qr_apply_q_device.restype = i
     lib.svdj_ring_phase_device.argtypes = [vp, sz, sz, sz, vp, vp, sz, vp, vp, sz, i, i, dbl, i, vp, vp]
     lib.svdj_ring_phase_device.restype = i
     lib.svdj_ring_finalize_device.argtypes = [vp, sz, sz, vp, sz, vp, i, vp]

@@ -19,10 +19,14 @@
 #include <vector>
 
 #include "svdj_common.cuh"
+#include "svdj_qr.cuh"
 
 namespace svdj {
 
 static thread_local char g_error[512] = "";
+
+// What opts.precondition < 0 resolves to (DESIGN.md section 5 has the measurements behind it)
+static constexpr int kAutoPrecondition = 0;
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -30,6 +34,8 @@ void set_error(const char *fmt, ...) {
   vsnprintf(g_error, sizeof(g_error), fmt, ap);
   va_end(ap);
 }
+
+void clear_error() { g_error[0] = 0; }
 
 static double now_s() {
   using namespace std::chrono;
@@ -169,14 +175,21 @@ struct DeviceGuard {
   }
 };
 
-static svdj_opts resolve_opts(const svdj_opts *in, size_t m) {
+// Default threshold of the relative test: LAPACK dgesvj's CTOL -- sqrt(m) when singular vectors are wanted (the
+// columns must come out orthogonal to working precision: |U^T U - I| <= 10 n eps needs cosines ~ sqrt(m) eps,
+// with m eps a 1,048,576-row input ends at 1e-10), m when only the singular values are.
+double default_tol(size_t m, int jobu, int jobv) {
+  const double mm = (double)(m ? m : 1);
+  const bool vectors = (jobu != SVDJ_NOVEC) || (jobv != SVDJ_NOVEC);
+  return (vectors ? std::sqrt(mm) : mm) * 0x1p-53;
+}
+
+static svdj_opts resolve_opts(const svdj_opts *in, size_t m, int jobu, int jobv) {
   svdj_opts o;
   svdj_default_opts(&o);
   if (in) o = *in;
   if (o.max_sweeps <= 0) o.max_sweeps = 60;
-  if (o.tol <= 0.0) {
-    o.tol = (o.threshold_mode == SVDJ_THRESH_ABS) ? 1e-16 : (double)(m ? m : 1) * 0x1p-53;
-  }
+  if (o.tol <= 0.0) o.tol = (o.threshold_mode == SVDJ_THRESH_ABS) ? 1e-16 : default_tol(m, jobu, jobv);
   return o;
 }
 
@@ -237,29 +250,6 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (int rc = d_counters.alloc(sizeof(SweepCounters) * (size_t)o.max_sweeps)) return rc;
   if (int rc = h_counters.alloc(sizeof(SweepCounters))) return rc;
   SVDJ_CUDA_TRY(cudaMemsetAsync(d_counters.p, 0, sizeof(SweepCounters) * (size_t)o.max_sweeps, stream));
-  DevBuf d_gpart, d_w, d_wflag, d_gcache;
-  if (block) {
-    // sized for either block width (the 32-wide kernels need more of everything per pair, for half the pairs)
-    size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
-    // (n + 256: room for the empty blocks the schedule may add, see below)
-    blk_scratch_sizes(m, n + 256, &gp, &wd, &fl);
-    blk32_scratch_sizes(m, n + 256, &gp2, &wd2, &fl2);
-    gp = std::max(gp, gp2);
-    wd = std::max(wd, wd2);
-    fl = std::max(fl, fl2);
-    if (int rc = d_gpart.alloc(sizeof(double) * gp)) return rc;
-    if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
-    if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
-    // per column block of 32: its Gram matrix as the last eigen-solve left it (8 KiB per block)
-    if (int rc = d_gcache.alloc(sizeof(double) * 1024 * (size_t)((n + 31) / 32 + 9))) return rc;
-  } else if (l1_uses_split(m, n)) {
-    if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
-  }
-
-  if (rotate_v) {
-    if (int rc = launch_set_identity(dV, ldv, vrows, n, stream, rs ? rs->v_row0 : 0)) return rc;
-    st.launches += 1;
-  }
 
   // block width: 16 by default; 32 on request (opts.block == 32 or SVDJ_BLOCK=32) when the layout allows it
   bool wide = false;
@@ -290,6 +280,31 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     if (nb >= 64) nb = (nb + 7u) & ~7u;
     else if (nb > 2 && (nb & 1u)) nb += 1u;
   }
+
+  // Scratch of the block path, sized for exactly the kernels and the (padded) block count that will run: the
+  // number of row splits of the Gram kernel is not monotonic in the number of pairs, so a size worked out for
+  // any other block count can be too small.  The launchers check the capacity again (BlockArgs::gpart_capacity).
+  DevBuf d_gpart, d_w, d_wflag, d_gcache;
+  size_t gpart_doubles = 0;
+  if (block) {
+    size_t wd = 0, fl = 0;
+    (wide ? blk32_scratch_sizes : blk_scratch_sizes)(m, nb, &gpart_doubles, &wd, &fl);
+    if (int rc = d_gpart.alloc(sizeof(double) * gpart_doubles)) return rc;
+    if (int rc = d_w.alloc(sizeof(double) * wd)) return rc;
+    if (int rc = d_wflag.alloc(sizeof(int) * fl)) return rc;
+    // per column block of 32: its Gram matrix as the last eigen-solve left it (8 KiB per block)
+    if (wide) {
+      if (int rc = d_gcache.alloc(sizeof(double) * 1024 * (size_t)nb)) return rc;
+    }
+  } else if (l1_uses_split(m, n)) {
+    if (int rc = d_scratch.alloc(sizeof(double) * l1_scratch_doubles(m, n))) return rc;
+  }
+
+  if (rotate_v) {
+    if (int rc = launch_set_identity(dV, ldv, vrows, n, stream, rs ? rs->v_row0 : 0)) return rc;
+    st.launches += 1;
+  }
+
   const unsigned steps = (unsigned)svdj_num_steps(block ? nb : n);
   // column pairs looked at per step: n/2 on the level-1 path, 496 (b = 16) or 2016 (b = 32) per block pair
   const unsigned long long pairs_per_step =
@@ -327,6 +342,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
       if (const char *e2 = std::getenv("SVDJ_SORT")) b.sort_cols = std::atoi(e2);
     }
   }
+  b.gpart_capacity = gpart_doubles;
   b.tol = o.tol;
   b.threshold_mode = o.threshold_mode;
   // One cyclic sweep of the small eigen-solve per visit below n = 8192, two from there on: a converged inner
@@ -382,7 +398,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
     if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
     if (rs) {  // global column norms: sum of the ranks' squares
       if (int rc = launch_square(d_norms.as<double>(), n, stream)) return rc;
-      if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) return SVDJ_ERR_CUDA;
+      if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) {
+        set_error("row-sharded solve: the caller's all-reduce (column norms) returned %d", rc);
+        return SVDJ_ERR_CUDA;
+      }
       if (int rc = launch_sqrt(d_norms.as<double>(), n, stream)) return rc;
     }
     std::vector<double> hn(n);
@@ -402,7 +421,7 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
       set_error("row-sharded solve: needs the 64-column block path (n >= 128, 16-byte aligned columns, even ld)");
       return SVDJ_ERR_UNSUPPORTED;
     }
-    const size_t gd = blk32_gred_doubles(n + 256);
+    const size_t gd = blk32_gred_doubles(nb);
     if (int rc = d_gred.alloc(sizeof(double) * gd)) return rc;
     SVDJ_CUDA_TRY(cudaMemsetAsync(d_gred.p, 0, sizeof(double) * gd, stream));
     row_hook.fn = rs->fn;
@@ -486,7 +505,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
   if (rs) {  // sigma_k^2 = sum over the ranks of the squared norms of their rows of column k
     if (int rc = launch_square(d_norms.as<double>(), n, stream)) return rc;
-    if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) return SVDJ_ERR_CUDA;
+    if (int rc = rs->fn(rs->ctx, d_norms.as<double>(), n, stream)) {
+      set_error("row-sharded solve: the caller's all-reduce (singular values) returned %d", rc);
+      return SVDJ_ERR_CUDA;
+    }
     if (int rc = launch_sqrt(d_norms.as<double>(), n, stream)) return rc;
   }
   st.launches += 1;
@@ -553,6 +575,151 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   return SVDJ_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Preconditioned solve (svdj_opts.precondition; Drmac & Veselic).  One-sided Jacobi needs dozens of sweeps when the
+// singular values are strongly graded but the columns are not (8192^2 with cond 1e12: more than 60).  Remedy, all of it
+// on the device with this library's own kernels (svdj_qr.cu):
+//   1. de Rijk pre-sort: columns by decreasing norm (a cheap stand-in for column pivoting),  A P
+//   2. A P = Q1 R1 (blocked Householder)                    [steps = 2:  R1^T = Q2 R2 once more]
+//   3. one-sided Jacobi on L = R1^T:  L J = W diag(s)        [steps = 2:  on L = R2^T]
+//   4. steps = 1:  A P = Q1 R1 = Q1 J s W^T          =>  U = Q1 [J; 0],  V = P W
+//      steps = 2:  R1 = R2^T Q2^T = (W s J^T) Q2^T   =>  U = Q1 [W; 0],  V = P Q2 J
+// The Jacobi iteration accumulates straight into the buffers the caller gave us where the layout allows it; the
+// Householder vectors need one m x n work buffer.  Requires m >= n.
+// ---------------------------------------------------------------------------------------------------------
+static size_t round16(size_t x) { return (x + 15) & ~size_t(15); }
+
+static int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
+                         size_t ldv, int qr_steps, const svdj_opts &o, svdj_stats &st, cudaStream_t stream) {
+  const bool want_u = (jobu != SVDJ_NOVEC), want_v = (jobv != SVDJ_NOVEC);
+  Event e0, e1, e2, e3;
+  if (int rc = e0.create()) return rc;
+  if (int rc = e1.create()) return rc;
+  if (int rc = e2.create()) return rc;
+  if (int rc = e3.create()) return rc;
+  SVDJ_CUDA_TRY(cudaEventRecord(e0.e, stream));
+  unsigned long long launches = 0;
+
+  // 1. column norms -> permutation (n doubles to the host and n indices back)
+  DevBuf d_norms, d_perm, d_Y, d_T1, d_T2, d_qrs, d_L, d_B1, d_J;
+  if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+  if (int rc = d_perm.alloc(sizeof(unsigned) * n)) return rc;
+  if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+  std::vector<double> hn(n);
+  SVDJ_CUDA_TRY(cudaMemcpyAsync(hn.data(), d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+  std::vector<unsigned> perm(n);
+  std::iota(perm.begin(), perm.end(), 0u);
+  std::stable_sort(perm.begin(), perm.end(), [&hn](unsigned x, unsigned y) { return hn[x] > hn[y]; });
+  SVDJ_CUDA_TRY(cudaMemcpyAsync(d_perm.p, perm.data(), sizeof(unsigned) * n, cudaMemcpyHostToDevice, stream));
+
+  // 2. Y = A P, factored in place
+  const size_t ldy = round16(m);
+  const size_t np = qr_num_panels(n);
+  if (int rc = d_Y.alloc(sizeof(double) * ldy * n)) return rc;
+  if (int rc = d_T1.alloc(sizeof(double) * 1024 * np)) return rc;
+  if (int rc = d_qrs.alloc(qr_scratch_bytes(n))) return rc;
+  if (int rc = launch_gather_columns(dA, lda, d_Y.as<double>(), ldy, m, n, d_perm.as<unsigned>(), nullptr, 0, stream))
+    return rc;
+  launches += 2;
+  if (int rc = qr_factor(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), d_qrs.p, stream, &launches)) return rc;
+
+  // 3. L = R^T (n x n lower triangular, one zero pad row when n is odd so that the vectorised kernels apply)
+  const size_t rows_l = (n + 1) & ~size_t(1);
+  const size_t ldl = round16(rows_l);
+  if (int rc = d_L.alloc(sizeof(double) * ldl * n)) return rc;
+  if (qr_steps >= 2) {
+    if (int rc = d_B1.alloc(sizeof(double) * ldl * n)) return rc;
+    if (int rc = d_T2.alloc(sizeof(double) * 1024 * np)) return rc;
+    if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_B1.as<double>(), ldl, n, stream)) return rc;
+    if (int rc = qr_factor(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), d_qrs.p, stream, &launches)) return rc;
+    if (int rc = qr_transpose_r(d_B1.as<double>(), ldl, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
+    launches += 2;
+  } else {
+    if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
+    launches += 1;
+  }
+
+  // Where the Jacobi iteration accumulates its rotations J.  steps = 1: J becomes U after Q1 is applied, so it grows
+  // in the top n rows of the caller's A (whose contents now live in Y); steps = 2: J becomes V after Q2, in a
+  // work buffer.
+  double *J = nullptr;
+  size_t ldj = 0, jrows = n;
+  const bool need_j = (qr_steps >= 2) ? want_v : want_u;
+  const bool need_w = (qr_steps >= 2) ? want_u : want_v;
+  if (qr_steps >= 2) {
+    if (need_j) {
+      if (int rc = d_J.alloc(sizeof(double) * ldl * n)) return rc;
+      J = d_J.as<double>();
+      ldj = ldl;
+      jrows = rows_l;
+    }
+  } else if (need_j) {
+    SVDJ_CUDA_TRY(cudaMemset2DAsync(dA, lda * sizeof(double), 0, m * sizeof(double), n, stream));
+    J = dA;
+    ldj = lda;
+    jrows = (m >= rows_l) ? rows_l : n;
+  }
+  SVDJ_CUDA_TRY(cudaEventRecord(e1.e, stream));
+
+  svdj_opts oi = o;
+  oi.precondition = 0;
+  const int rc_inner = solve_on_device(need_w ? SVDJ_ALLVEC : SVDJ_NOVEC, need_j ? SVDJ_ALLVEC : SVDJ_NOVEC, rows_l, n,
+                                       d_L.as<double>(), ldl, ds, J, ldj, need_j ? jrows : n, oi, st, stream);
+  if (rc_inner != SVDJ_OK && rc_inner != SVDJ_NOT_CONVERGED) return rc_inner;
+  SVDJ_CUDA_TRY(cudaEventRecord(e2.e, stream));
+
+  // 4. back to the caller's U and V
+  double *W = d_L.as<double>();  // normalised columns of L J: the left singular vectors of L, sigma-sorted
+  if (qr_steps >= 2) {
+    if (want_v) {  // V = P (Q2 J)
+      if (int rc = qr_apply_q(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), J, ldj, n, stream, &launches)) return rc;
+      if (int rc = qr_scatter_rows(J, ldj, dV, ldv, n, n, d_perm.as<unsigned>(), stream)) return rc;
+      launches += 1;
+    }
+    if (want_u) {  // U = Q1 [W; 0]
+      SVDJ_CUDA_TRY(cudaMemset2DAsync(dA, lda * sizeof(double), 0, m * sizeof(double), n, stream));
+      SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dA, lda * sizeof(double), W, ldl * sizeof(double), n * sizeof(double), n,
+                                      cudaMemcpyDeviceToDevice, stream));
+      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, stream, &launches)) return rc;
+    }
+  } else {
+    if (want_v) {  // V = P W
+      if (int rc = qr_scatter_rows(W, ldl, dV, ldv, n, n, d_perm.as<unsigned>(), stream)) return rc;
+      launches += 1;
+    }
+    if (want_u) {  // U = Q1 [J; 0], in place
+      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, stream, &launches)) return rc;
+    }
+  }
+  SVDJ_CUDA_TRY(cudaEventRecord(e3.e, stream));
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+  float ms01 = 0.f, ms23 = 0.f;
+  SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms01, e0.e, e1.e));
+  SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms23, e2.e, e3.e));
+  st.seconds_precond = (ms01 + ms23) * 1e-3;
+  st.precondition = qr_steps;
+  st.launches += launches;
+  return rc_inner;
+}
+
+// Which front-end runs.  opts.precondition: 0 none, 1 / 2 QR steps, < 0 the library decides.  SVDJ_PRECOND overrides.
+static int precondition_steps(const svdj_opts &o, size_t m, size_t n) {
+  int want = o.precondition;
+  if (const char *env = std::getenv("SVDJ_PRECOND")) want = std::atoi(env);
+  const bool possible = m >= n && n >= 64 && qr_supported(m, n) && o.threshold_mode == SVDJ_THRESH_REL;
+  if (!possible) return 0;
+  if (want < 0) want = kAutoPrecondition;
+  return want > 2 ? 2 : want;
+}
+
+static int solve_entry(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
+                       size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st, cudaStream_t stream) {
+  const int steps = (m == 0 || n == 0) ? 0 : precondition_steps(o, m, n);
+  if (steps == 0) return solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, vrows, o, st, stream);
+  return solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, o, st, stream);
+}
+
 }  // namespace svdj
 
 using namespace svdj;
@@ -568,7 +735,7 @@ void svdj_default_opts(svdj_opts *o) {
   o->threshold_mode = SVDJ_THRESH_REL;
   o->block = 0;
   o->device = -1;
-  o->use_graph = -1;
+  o->precondition = -1;
 }
 
 const char *svdj_last_error(void) { return g_error; }
@@ -629,7 +796,7 @@ int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double
   }
   if (allreduce == nullptr) return -15;
   const double t0 = now_s();
-  svdj_opts o = resolve_opts(opts, m_local);
+  svdj_opts o = resolve_opts(opts, m_local, jobu, jobv);
   o.variant = SVDJ_VARIANT_BLOCK;
   o.block = 32;
   o.threshold_mode = SVDJ_THRESH_REL;
@@ -644,6 +811,38 @@ int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double
 
 size_t svdj_step_scratch_doubles(size_t m, size_t n) { return l1_scratch_doubles(m, n); }
 
+size_t svdj_qr_tfactor_doubles(size_t n) { return 1024 * qr_num_panels(n); }
+
+int svdj_qr_factor_device(size_t m, size_t n, double *dY, size_t ld, double *dT, void *stream) {
+  clear_error();
+  if (m > 0x7fffffffu) return -1;
+  if (n > 0x7fffffffu || n > m) return -2;
+  if (dY == nullptr && m * n > 0) return -3;
+  if (ld < m) return -4;
+  if (dT == nullptr && n > 0) return -5;
+  if (n == 0) return SVDJ_OK;
+  DevBuf scratch;
+  if (int rc = scratch.alloc(qr_scratch_bytes(n))) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int rc = qr_factor(dY, ld, m, n, dT, scratch.p, st, nullptr)) return rc;
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(st));  // the scratch goes back to the pool on return
+  return SVDJ_OK;
+}
+
+int svdj_qr_apply_q_device(size_t m, size_t n, const double *dY, size_t ld, const double *dT, double *dC, size_t ldc,
+                           size_t ncols, void *stream) {
+  clear_error();
+  if (m > 0x7fffffffu) return -1;
+  if (n > 0x7fffffffu || n > m) return -2;
+  if (dY == nullptr && m * n > 0) return -3;
+  if (ld < m) return -4;
+  if (dT == nullptr && n > 0) return -5;
+  if (dC == nullptr && m * ncols > 0) return -6;
+  if (ldc < m) return -7;
+  if (ncols > 0x7fffffffu) return -8;
+  return qr_apply_q(dY, ld, m, n, dT, dC, ldc, ncols, static_cast<cudaStream_t>(stream), nullptr);
+}
+
 int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
                        size_t ldv, const svdj_opts *opts, svdj_stats *stats, void *stream) {
   g_error[0] = 0;
@@ -655,10 +854,10 @@ int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_
     return bad;
   }
   const double t0 = now_s();
-  svdj_opts o = resolve_opts(opts, m);
+  svdj_opts o = resolve_opts(opts, m, jobu, jobv);
   DeviceGuard guard;
   if (int rc = guard.enter(o.device)) return rc;
-  int rc = solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, n, o, st, static_cast<cudaStream_t>(stream));
+  int rc = solve_entry(jobu, jobv, m, n, dA, lda, ds, dV, ldv, n, o, st, static_cast<cudaStream_t>(stream));
   st.seconds_total = now_s() - t0;
   return rc;
 }
@@ -674,7 +873,7 @@ int svdj_dgesvd(int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, d
     return bad;
   }
   const double t0 = now_s();
-  svdj_opts o = resolve_opts(opts, m);
+  svdj_opts o = resolve_opts(opts, m, jobu, jobv);
   DeviceGuard guard;
   if (int rc = guard.enter(o.device)) return rc;
   const size_t mn = std::min(m, n);
@@ -711,8 +910,8 @@ int svdj_dgesvd(int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, d
   st.seconds_h2d = now_s() - t;
 
   // V is n x n; with n odd the kernels see n_pad rows (the identity init writes the pad row as zero)
-  int rc = solve_on_device(jobu, jobv, m_pad, n, dA.as<double>(), lda_d, ds.as<double>(), dV.as<double>(), ldv_d,
-                           n_pad, o, st, stream);
+  int rc = solve_entry(jobu, jobv, m_pad, n, dA.as<double>(), lda_d, ds.as<double>(), dV.as<double>(), ldv_d, n_pad,
+                       o, st, stream);
   if (rc != SVDJ_OK && rc != SVDJ_NOT_CONVERGED) return rc;
 
   t = now_s();

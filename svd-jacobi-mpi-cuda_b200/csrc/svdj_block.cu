@@ -668,8 +668,7 @@ static unsigned gram_splits(size_t m, unsigned pairs) {
   return (unsigned)want;
 }
 
-void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
-  const unsigned nb = blk_num_blocks(n);
+void blk_scratch_sizes(size_t m, unsigned nb, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
   const unsigned pairs = nb / 2;
   *gpart_doubles = (size_t)pairs * gram_splits(m, pairs) * kGramPart;
   *w_doubles = (size_t)pairs * kD * kD;
@@ -710,6 +709,11 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
     a.cross_only = (!always_full && (a.sched == 1 || (k > 1 && a.nb % 2 == 0))) ? 1 : 0;
   }
   const unsigned splits = gram_splits(a.m, pairs);
+  if (a.gpart_capacity != 0 && (size_t)pairs * splits * kGramPart > a.gpart_capacity) {
+    set_error("block step: %u pairs x %u row splits need %zu doubles of partial Gram matrices, the buffer holds %zu",
+              pairs, splits, (size_t)pairs * splits * kGramPart, a.gpart_capacity);
+    return SVDJ_ERR_ALLOC;
+  }
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + 3u) & ~3u;  // k-steps are 4 rows
   const bool aligned = (a.lda % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.A) & 15) == 0) &&
@@ -721,10 +725,19 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
   (void)st_aligned;
   const bool staged = aligned && pairs <= (unsigned)kMaxCompactPairs && !blk_force_plain_update();
   constexpr size_t kStageSmem = sizeof(double) * kUpdStages * kTileDoubles;
+  static DeviceOnce once;  // the shared-memory opt-in is per device
+  int sm_count = 148;
+  SVDJ_CUDA_TRY(once.run(
+      [] {
+        cudaError_t e = cudaFuncSetAttribute(blk_gram_staged_kernel<kUpdStages>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStageSmem);
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(blk_update_staged_kernel<kUpdStages>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)kStageSmem);
+        return e;
+      },
+      &sm_count));
   if (staged) {
-    static const cudaError_t gattr = cudaFuncSetAttribute(blk_gram_staged_kernel<kUpdStages>,
-                                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStageSmem);
-    SVDJ_CUDA_TRY(gattr);
     rps = (rps + kTileRows - 1) / kTileRows * kTileRows;  // whole tiles per split
     SVDJ_CUDA_TRY(launch_k(blk_gram_staged_kernel<kUpdStages>, dim3(pairs, splits), 128, kStageSmem, st, a, k, rps, gpart));
   } else {
@@ -737,15 +750,7 @@ int blk_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wb
   if (usplits > ucap) usplits = ucap;
   if (usplits < 1) usplits = 1;
   if (staged) {
-    static const int sm_count = [] {
-      int dev = 0, n = 148;
-      if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-      return n;
-    }();
     constexpr size_t smem = kStageSmem;
-    static const cudaError_t attr = cudaFuncSetAttribute(blk_update_staged_kernel<kUpdStages>,
-                                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    SVDJ_CUDA_TRY(attr);
     if (probe) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
     SVDJ_CUDA_TRY(launch_k(blk_update_staged_kernel<kUpdStages>, dim3(sm_count * kUpdCtasPerSm), 128, smem, st, a, k, wbuf,
                            wflag, pairs, probe ? probe->active_pairs : nullptr));

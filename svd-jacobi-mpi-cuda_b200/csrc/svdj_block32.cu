@@ -715,8 +715,7 @@ static unsigned gram32_splits(size_t m, unsigned pairs) {
   return (unsigned)((tiles + tiles_per_split - 1) / tiles_per_split);
 }
 
-void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
-  const unsigned nb = blk32_num_blocks(n);
+void blk32_scratch_sizes(size_t m, unsigned nb, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints) {
   const unsigned pairs = nb / 2;
   *gpart_doubles = (size_t)pairs * gram32_splits(m, pairs) * kGramPart32;
   *w_doubles = (size_t)pairs * kD64 * kD64;
@@ -731,7 +730,7 @@ bool blk32_supported(const BlockArgs &a) {
   return aligned && aligned2 && (a.nb / 2) <= (unsigned)kMaxPairs32 && a.nb >= 2;
 }
 
-size_t blk32_gred_doubles(size_t n) { return (size_t)(blk32_num_blocks(n) / 2 + 8) * kGramPart32; }
+size_t blk32_gred_doubles(unsigned nb) { return (size_t)(nb / 2) * kGramPart32; }
 
 int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
                       unsigned long long *launches, const BlockProbe *probe, const RowHook *rows) {
@@ -763,25 +762,28 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   // The Gram cache needs every block in a pair of the first step, which refreshes it
   if (a.gcache != nullptr && (a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
   a.gram_mode = (a.gcache == nullptr) ? 0 : (k == 1 ? 1 : 2);
-  static const cudaError_t attrs = [] {
-    cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(blk32_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(blk32_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kE32Smem);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(blk32_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kU32Smem);
-    return e;
-  }();
-  SVDJ_CUDA_TRY(attrs);
-  static const int sm_count = [] {
-    int dev = 0, n = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    return n;
-  }();
+  static DeviceOnce once;  // the shared-memory opt-in is per device
+  int sm_count = 148;
+  SVDJ_CUDA_TRY(once.run(
+      [] {
+        cudaError_t e = cudaFuncSetAttribute(blk32_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(blk32_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(sizeof(double) * kG32Stages * kG32TileDoubles));
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(blk32_eig_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kE32Smem);
+        if (e == cudaSuccess)
+          e = cudaFuncSetAttribute(blk32_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kU32Smem);
+        return e;
+      },
+      &sm_count));
   const unsigned splits = gram32_splits(a.m, pairs);
+  if (a.gpart_capacity != 0 && (size_t)pairs * splits * kGramPart32 > a.gpart_capacity) {
+    set_error("block step: %u pairs x %u row splits need %zu doubles of partial Gram matrices, the buffer holds %zu",
+              pairs, splits, (size_t)pairs * splits * kGramPart32, a.gpart_capacity);
+    return SVDJ_ERR_ALLOC;
+  }
   unsigned rps = (a.m + splits - 1) / splits;
   rps = (rps + kG32Rows - 1) / kG32Rows * kG32Rows;
   // SVDJ_PROBE_KERNEL=1|2 moves the probe events from the update kernel to K1 or K2 (profiling aid)

@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdlib>
 #include <utility>
 #include <stddef.h>
@@ -15,6 +16,7 @@ namespace svdj {
 // error plumbing: every CUDA call is checked (the reference checks none)
 // ---------------------------------------------------------------------------------------------
 void set_error(const char *fmt, ...);
+void clear_error();  // empties the calling thread's error text (every entry point starts with it)
 
 #define SVDJ_CUDA_TRY(expr)                                                                   \
   do {                                                                                        \
@@ -24,6 +26,36 @@ void set_error(const char *fmt, ...);
       return SVDJ_ERR_CUDA;                                                                   \
     }                                                                                         \
   } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Per-device set-up.  cudaFuncSetAttribute (the opt-in to more than 48 KB of dynamic shared memory) and the SM
+// count belong to a DEVICE, not to the process: a process that drives several GPUs (svdj_opts.device, the
+// multi-GPU driver in svdj_mg.cu) must repeat the set-up on each of them.  `DeviceOnce` remembers, per device
+// ordinal, that `fn` succeeded there; a failure is returned and retried on the next call.
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxDevices = 64;
+struct DeviceOnce {
+  std::atomic<int> done[kMaxDevices];
+  int sm_count[kMaxDevices];
+  template <class F>
+  cudaError_t run(F &&fn, int *sms = nullptr) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    if (!done[dev].load(std::memory_order_acquire)) {
+      e = fn();
+      if (e != cudaSuccess) return e;
+      int n = 0;
+      e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+      if (e != cudaSuccess) return e;
+      sm_count[dev] = n;
+      done[dev].store(1, std::memory_order_release);
+    }
+    if (sms) *sms = sm_count[dev];
+    return cudaSuccess;
+  }
+};
 
 // ---------------------------------------------------------------------------------------------
 // per-sweep counters kept on the device (what lib/JacobiMethods.cu:462 computes and drops)
@@ -238,6 +270,8 @@ struct BlockArgs {
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
   SweepCounters *counters;  // may be null
   double floor2 = 0.0;      // columns with squared norm <= floor2 are treated as zero (never rotated)
+  // doubles the caller's partial-Gram buffer holds; the launchers refuse a step that needs more (0 = unchecked)
+  size_t gpart_capacity = 0;
 };
 // Optional timing of the update kernel (the dominant, HBM-bound one) of a step: events recorded around it
 // and a device counter that receives the number of block pairs it really updated.
@@ -283,7 +317,8 @@ struct BlockProbe {
   unsigned long long *active_pairs = nullptr;
 };
 unsigned blk_num_blocks(size_t n);
-void blk_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
+// scratch of a step over nb column blocks (nb as the launcher will see it, padding included)
+void blk_scratch_sizes(size_t m, unsigned nb, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
 // k = 1-based step of the round-robin ordering over the nb blocks
 struct RowHook;
 int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
@@ -291,11 +326,12 @@ int blk_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf,
 
 // The same step with column blocks of 32 (svdj_block32.cu); single buffer, aligned layouts only.
 unsigned blk32_num_blocks(size_t n);
-void blk32_scratch_sizes(size_t m, size_t n, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
+void blk32_scratch_sizes(size_t m, unsigned nb, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
 bool blk32_supported(const BlockArgs &a);
 int blk32_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbuf, int *wflag, cudaStream_t st,
                       unsigned long long *launches, const BlockProbe *probe = nullptr, const RowHook *rows = nullptr);
-size_t blk32_gred_doubles(size_t n);
+size_t blk32_gred_doubles(unsigned nb);  // all-reduce buffer of the row-sharded driver for nb column blocks
+double default_tol(size_t m, int jobu, int jobv);
 
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0 = 0);

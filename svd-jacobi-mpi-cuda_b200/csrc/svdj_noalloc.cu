@@ -35,7 +35,6 @@ static constexpr size_t kSplitScratchMaxDoubles = SVDJ_NOALLOC_MAX_SCRATCH_DOUBL
 // reach it).  The address the kernels get comes from cudaGetSymbolAddress below.
 static __device__ __align__(256) double g_split_scratch[kSplitScratchMaxDoubles];
 
-static constexpr int kMaxDevices = 64;
 static std::mutex g_setup_mutex;
 static double *g_scratch_addr[kMaxDevices] = {};  // per device ordinal, filled on first use
 
@@ -70,13 +69,19 @@ extern "C" {
 int svdj_step_device_noalloc(size_t m, size_t n, double *dA, size_t lda, double *dV, size_t ldv, int rotate_v,
                              size_t step, double tol, int threshold_mode, unsigned long long *d_counters,
                              void *stream) {
-  if (m == 0 || m > 0x7fffffffu) return -1;
-  if (n > 0x7fffffffu) return -2;
-  if (dA == nullptr) return -3;
-  if (lda < m) return -4;
-  if (rotate_v && dV == nullptr) return -5;
-  if (rotate_v && ldv < n) return -6;
-  if (step >= svdj_num_steps(n)) return -8;
+  clear_error();
+  int bad = 0;
+  if (m == 0 || m > 0x7fffffffu) bad = -1;
+  else if (n > 0x7fffffffu) bad = -2;
+  else if (dA == nullptr) bad = -3;
+  else if (lda < m) bad = -4;
+  else if (rotate_v && dV == nullptr) bad = -5;
+  else if (rotate_v && ldv < n) bad = -6;
+  else if (step >= svdj_num_steps(n)) bad = -8;
+  if (bad) {
+    set_error("svdj_step_device_noalloc: argument %d is invalid", -bad);
+    return bad;
+  }
   const size_t need = l1_scratch_doubles(m, n);
   if (need > kSplitScratchMaxDoubles) {
     set_error("svdj_step_device_noalloc: a %zu x %zu step needs %zu doubles of scratch, the built-in array holds %zu; "

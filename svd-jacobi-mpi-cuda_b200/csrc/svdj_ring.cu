@@ -24,6 +24,8 @@ struct RingWorkspace {
   int *wflag = nullptr;
   double *norms = nullptr;
   double *gcache = nullptr;  // 64-column kernels: Gram matrix of every local column block of 32
+  size_t gpart_doubles = 0;  // capacity of gpart (checked by the launchers)
+  double floor2 = 0.0;       // squared norm below which a column is numerically zero (svdj_ring_ws_set_floor)
 };
 
 static void ws_free(RingWorkspace *w) {
@@ -52,9 +54,10 @@ int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out) {
   w->m = m;
   w->ncols = ncols_local;
   size_t gp = 0, wd = 0, fl = 0, gp2 = 0, wd2 = 0, fl2 = 0;
-  blk_scratch_sizes(m, ncols_local, &gp, &wd, &fl);
-  blk32_scratch_sizes(m, ncols_local, &gp2, &wd2, &fl2);  // either block width
+  blk_scratch_sizes(m, blk_num_blocks(ncols_local), &gp, &wd, &fl);
+  blk32_scratch_sizes(m, blk32_num_blocks(ncols_local), &gp2, &wd2, &fl2);  // either block width
   gp = gp > gp2 ? gp : gp2;
+  w->gpart_doubles = gp;
   wd = wd > wd2 ? wd : wd2;
   fl = fl > fl2 ? fl : fl2;
   cudaError_t e = cudaMalloc(&w->gpart, sizeof(double) * gp);
@@ -69,6 +72,14 @@ int svdj_ring_ws_create(size_t m, size_t ncols_local, void **ws_out) {
     return SVDJ_ERR_ALLOC;
   }
   *ws_out = w;
+  return SVDJ_OK;
+}
+
+int svdj_ring_ws_set_floor(void *ws, double floor_norm) {
+  RingWorkspace *W = static_cast<RingWorkspace *>(ws);
+  if (W == nullptr) return -1;
+  if (!(floor_norm >= 0.0)) return -2;
+  W->floor2 = floor_norm * floor_norm;
   return SVDJ_OK;
 }
 
@@ -112,6 +123,8 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
   b.threshold_mode = SVDJ_THRESH_REL;
   b.max_inner_sweeps = inner_sweeps > 0 ? inner_sweeps : 2;
   b.counters = reinterpret_cast<SweepCounters *>(d_counters);
+  b.floor2 = W->floor2;
+  b.gpart_capacity = W->gpart_doubles;
   if (wide) {
     wide = blk32_supported(b);
     if (!wide) b.nb = blk_num_blocks(2 * w);

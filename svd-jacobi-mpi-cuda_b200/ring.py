@@ -233,7 +233,7 @@ class RingSolver:
         self.lda = (m + 15) // 16 * 16   # 128-byte columns
         self.ldv = (n + 15) // 16 * 16
         self.device = device
-        self.tol = tol if tol is not None else m * 2.0 ** -53
+        self.tol = tol if tol is not None else m ** 0.5 * 2.0 ** -53  # dgesvj CTOL when vectors are wanted
         self.max_sweeps = max_sweeps
         self.backend = backend if backend is not None else GpuBackend(m, n, self.w, self.lda, self.ldv, self.tol,
                                                                     inner_sweeps)

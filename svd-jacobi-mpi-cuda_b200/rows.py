@@ -72,7 +72,7 @@ class RowShardSolver:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.row0, self.m_local = row_partition(m, self.P)[self.rank]
         self.v_row0, self.v_local = row_partition(n, self.P, multiple=1)[self.rank]
-        self.tol = tol if tol is not None else m * 2.0 ** -53
+        self.tol = tol if tol is not None else m ** 0.5 * 2.0 ** -53  # dgesvj CTOL when vectors are wanted
         self.max_sweeps = max_sweeps
         self.lda = (self.m_local + 15) // 16 * 16           # 128-byte columns: aligned, even
         self.ldv = (self.v_local + 15) // 16 * 16

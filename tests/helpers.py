@@ -69,7 +69,7 @@ def oracle_svd(A0: np.ndarray, mode=ORACLE_REL, threshold=None, max_sweeps=60, s
     """Runs the oracle on a copy of A0; returns (U, s, V, stats, rc)."""
     m, n = A0.shape
     if threshold is None:
-        threshold = m * 2.0 ** -53 if mode == ORACLE_REL else 1e-16
+        threshold = m ** 0.5 * 2.0 ** -53 if mode == ORACLE_REL else 1e-16  # dgesvj CTOL with vectors
     A = np.array(A0, dtype=np.float64, order="F", copy=True)
     s = np.zeros(min(m, n))
     V = np.zeros((n, n), order="F")
