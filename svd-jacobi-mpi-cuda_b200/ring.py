@@ -30,6 +30,7 @@ a stand-in backend; the product backend is :class:`GpuBackend` and there is no C
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
@@ -235,6 +236,8 @@ class RingSolver:
         self.device = device
         self.tol = tol if tol is not None else m ** 0.5 * 2.0 ** -53  # dgesvj CTOL when vectors are wanted
         self.max_sweeps = max_sweeps
+        # the quadratic-convergence stop assumes separated singular values (csrc/svdj_api.cu); off unless asked for
+        self.early_stop = os.environ.get("SVDJ_EARLY_STOP", "0") == "1"
         self.backend = backend if backend is not None else GpuBackend(m, n, self.w, self.lda, self.ldv, self.tol,
                                                                     inner_sweeps)
         fused = self.exchange == "fused"
@@ -392,7 +395,7 @@ class RingSolver:
             last_off = float(host[1:2].view(torch.float64)[0])
             applied_total += applied
             sweeps = sweep + 1
-            if applied == 0 or quadratic_stop(applied, last_off, self.tol):
+            if applied == 0 or (self.early_stop and quadratic_stop(applied, last_off, self.tol)):
                 converged = True
                 break
         return {"sweeps": sweeps, "converged": converged, "applied": applied_total, "last_offdiag": last_off,
