@@ -230,6 +230,51 @@ int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double
                             svdj_stats *stats, void *stream, svdj_allreduce_fn allreduce, void *ctx);
 
 /*
+ * The multi-GPU solve as ONE collective call, like the reference's omp_mpi_cuda_dgesvd_local_matrices (main.cu:1587:
+ * every rank calls, the matrix is valid on rank 0 only, main.cu:1455; rank and size are taken inside,
+ * lib/JacobiMethods.cu:209-211).  The host driver is C++ inside the library (csrc/svdj_mg.cu): 2P column blocks on a
+ * ring of P GPUs, the block move fused into the update kernel (peer stores over NVLink), rounds ordered by flags in
+ * peer memory, convergence data exchanged through peer mailboxes -- no collective library call inside a solve.
+ * It replaces the reference's per-step MPI_Send / MPI_Recv / MPI_Barrier star (main.cu:583-942).
+ *
+ * svdj_dgesvd_mg: single process, ngpus devices (devices[] = their ordinals, NULL = 0 .. ngpus-1).  Same contract
+ *   as svdj_dgesvd (host pointers, U in A, sigma sorted).  The ranks are threads inside the call; their buffers and
+ *   peer mappings are kept between calls (svdj_release_workspace frees them).  ngpus = 1 is svdj_dgesvd.
+ *
+ * svdj_mg_rank_*: one rank per process / GPU (e.g. under torchrun or mpirun).  The communicator needs one
+ *   operation, used at set-up only: allgather(ctx, send, recv, bytes) gathers `bytes` bytes of host memory from
+ *   every rank into recv in rank order (recv holds size * bytes) and returns 0 (MPI_Allgather on MPI_BYTE).  The
+ *   ranks then map each other's buffers through CUDA IPC.  svdj_mg_rank_create is collective and uses the calling
+ *   thread's current device; max_m x max_n bounds the problems the handle can solve.
+ *   svdj_mg_rank_dgesvd (host pointers) and svdj_mg_rank_dgesvd_device (device pointers on rank 0's GPU) are
+ *   collective: every rank calls with the same sizes, jobs and options; only rank 0's A, s, V are used, the other
+ *   ranks may pass NULL.  A rank that waits more than 60 s
+ *   (SVDJ_MG_TIMEOUT_S) for a peer gives up with SVDJ_ERR_CUDA instead of hanging its GPU.
+ * opts->precondition is not applied here (the QR front-end is single-GPU: factor on one GPU first if needed).
+ * svdj_mg_plan: host-side copy of the tournament the driver walks, for tests: after `round` moves, which block
+ *   (0 .. 2P-1) rank r holds as top / bottom and in which of its four buffers, and the transfers of the next move as
+ *   (src rank, src buffer, dst rank, dst buffer) quadruples (at most 2P-2).  It stands where the reference's
+ *   per-step rank assignment and packing stood (main.cu:526-580).
+ */
+typedef int (*svdj_allgather_fn)(void *ctx, const void *send, void *recv, size_t bytes);
+typedef struct svdj_mg_comm {
+  int rank;
+  int size;
+  svdj_allgather_fn allgather;
+  void *ctx;
+} svdj_mg_comm;
+int svdj_dgesvd_mg(int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, double *s, double *V, size_t ldv,
+                   const svdj_opts *opts, svdj_stats *stats, int ngpus, const int *devices);
+int svdj_mg_rank_create(const svdj_mg_comm *comm, size_t max_m, size_t max_n, void **handle);
+int svdj_mg_rank_destroy(void *handle);
+int svdj_mg_plan(int P, int round, int *top_block, int *bottom_block, int *top_buf, int *bottom_buf, int *transfers,
+                 int *ntransfers);
+int svdj_mg_rank_dgesvd(void *handle, int jobu, int jobv, size_t m, size_t n, double *A, size_t lda, double *s,
+                        double *V, size_t ldv, const svdj_opts *opts, svdj_stats *stats);
+int svdj_mg_rank_dgesvd_device(void *handle, int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda,
+                               double *ds, double *dV, size_t ldv, const svdj_opts *opts, svdj_stats *stats);
+
+/*
  * The QR front-end's building blocks on device buffers (what svdj_opts.precondition runs before and after the
  * sweeps).  The reference has no factorisation step: its doc block names tall inputs as the use-case
  * (lib/JacobiMethods.cu:12-14) and then sweeps the raw columns (main.cu:478-1384).
@@ -264,6 +309,9 @@ size_t svdj_block_schedule_step(size_t nb, int vranks, size_t step, size_t *pq);
  * reference allocates and frees its staging vectors on every call (main.cu:484-494, 1385-1392).
  * svdj_release_workspace() returns every idle pooled buffer to the driver. */
 int svdj_release_workspace(void);
+
+/* CUDA devices visible to this process (0 without a driver or device). */
+int svdj_device_count(void);
 
 /* Text of the most recent error on the calling thread ("" if none). */
 const char *svdj_last_error(void);

@@ -10,8 +10,13 @@
 // both at global scope (the copies main.cu calls) and in namespace Thesis (lib/JacobiMethods.cuh:44-62).
 // Same argument meaning: A column-major m x n in / U out in place, s = singular values, V = right
 // singular vectors (not transposed).  Error behaviour: the reference returns void and ignores every
-// failure; these throw std::runtime_error with the library's message instead of continuing silently,
-// except SVDJ_NOT_CONVERGED, which (like the reference) returns the current iterate.
+// failure; these throw std::runtime_error with the library's message instead of continuing silently.
+// SVDJ_NOT_CONVERGED returns the current iterate (the reference always returns after its one sweep) but says
+// so on stderr, and svdj_shim::last_status() reports the status of the calling thread's last solve.
+//
+// Several GPUs: the reference's MPI entry point is one collective call with the data on rank 0 (main.cu:1455,
+// 1587).  Here omp_mpi_cuda_dgesvd_local_matrices runs the in-library multi-GPU driver (svdj_dgesvd_mg) on
+// SVDJ_NGPUS devices of the calling process (environment; default 1, "all" = every visible GPU).
 //
 // Types: a translation unit that already has the reference's Matrix / MatrixMPI / SVD_OPTIONS
 // (e.g. main.cu itself, which defines them at main.cu:17-69 and :152-160) defines
@@ -20,6 +25,9 @@
 #pragma once
 
 #include <cstddef>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 
@@ -56,11 +64,44 @@ enum SVD_OPTIONS { AllVec = SVDJ_ALLVEC, SomeVec = SVDJ_SOMEVEC, NoVec = SVDJ_NO
 
 namespace svdj_shim {
 
+inline int &status_slot() {
+  static thread_local int status = SVDJ_OK;
+  return status;
+}
+// Status of the calling thread's most recent solve through this header (SVDJ_OK, SVDJ_NOT_CONVERGED, ...).
+inline int last_status() { return status_slot(); }
+
+inline void finish(int rc) {
+  status_slot() = rc;
+  if (rc == SVDJ_OK) return;
+  if (rc == SVDJ_NOT_CONVERGED) {
+    std::fprintf(stderr, "libsvdj: warning: max_sweeps reached, the returned factors are the current iterate, not a "
+                         "converged SVD (svdj_shim::last_status() == SVDJ_NOT_CONVERGED)\n");
+    return;
+  }
+  throw std::runtime_error("libsvdj: status " + std::to_string(rc) + ": " + svdj_last_error());
+}
+
 inline void solve(int jobu, int jobv, std::size_t m, std::size_t n, double *A, std::size_t lda, double *s,
                   double *V, std::size_t ldv, const svdj_opts *opts = nullptr, svdj_stats *stats = nullptr) {
-  const int rc = svdj_dgesvd(jobu, jobv, m, n, A, lda, s, V, ldv, opts, stats);
-  if (rc == SVDJ_OK || rc == SVDJ_NOT_CONVERGED) return;
-  throw std::runtime_error("libsvdj: status " + std::to_string(rc) + ": " + svdj_last_error());
+  finish(svdj_dgesvd(jobu, jobv, m, n, A, lda, s, V, ldv, opts, stats));
+}
+
+// SVDJ_NGPUS: how many GPUs of this process the distributed entry point uses
+inline int ngpus_from_env() {
+  const char *e = std::getenv("SVDJ_NGPUS");
+  if (e == nullptr || *e == 0) return 1;
+  if (!std::strcmp(e, "all")) return 0;
+  const int v = std::atoi(e);
+  return v < 1 ? 1 : v;
+}
+
+inline void solve_mg(int jobu, int jobv, std::size_t m, std::size_t n, double *A, std::size_t lda, double *s,
+                     double *V, std::size_t ldv, int ngpus, const svdj_opts *opts = nullptr,
+                     svdj_stats *stats = nullptr) {
+  if (ngpus == 0) ngpus = svdj_device_count();
+  if (ngpus <= 1) return solve(jobu, jobv, m, n, A, lda, s, V, ldv, opts, stats);
+  finish(svdj_dgesvd_mg(jobu, jobv, m, n, A, lda, s, V, ldv, opts, stats, ngpus, nullptr));
 }
 
 }  // namespace svdj_shim
@@ -73,12 +114,14 @@ inline void cuda_dgesvd_kernel(SVD_OPTIONS jobu, SVD_OPTIONS jobv, std::size_t m
 
 // main.cu:440.  In the reference this is a collective over MPI_COMM_WORLD in which only rank 0 holds
 // A, s and V (the other ranks pass default-constructed matrices, main.cu:1455).  Here the whole solve
-// runs on the GPU(s) of the calling process, so a call without data (elements == nullptr) returns at once.
+// runs on the GPU(s) of the calling process -- SVDJ_NGPUS of them, through the in-library multi-GPU driver --
+// so a call without data (elements == nullptr) returns at once.
 inline void omp_mpi_cuda_dgesvd_local_matrices(SVD_OPTIONS jobu, SVD_OPTIONS jobv, std::size_t m, std::size_t n,
                                                MatrixMPI &A, std::size_t lda, MatrixMPI &s, MatrixMPI &V,
                                                std::size_t ldv) {
   if (A.elements == nullptr) return;
-  svdj_shim::solve(static_cast<int>(jobu), static_cast<int>(jobv), m, n, A.elements, lda, s.elements, V.elements, ldv);
+  svdj_shim::solve_mg(static_cast<int>(jobu), static_cast<int>(jobv), m, n, A.elements, lda, s.elements, V.elements,
+                      ldv, svdj_shim::ngpus_from_env());
 }
 
 namespace Thesis {

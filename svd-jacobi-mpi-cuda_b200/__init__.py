@@ -39,6 +39,14 @@ class SvdjError(RuntimeError):
 AllreduceFn = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 
 
+# svdj_allgather_fn (svdj.h): gather `bytes` bytes of host memory from every rank into recv, in rank order
+AllgatherFn = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+class MgComm(C.Structure):
+    _fields_ = [("rank", C.c_int), ("size", C.c_int), ("allgather", AllgatherFn), ("ctx", C.c_void_p)]
+
+
 class Opts(C.Structure):
     _fields_ = [
         ("tol", C.c_double),
@@ -101,6 +109,13 @@ EXPORTS = (
     "svdj_ipc_export",
     "svdj_ipc_open",
     "svdj_ipc_close",
+    "svdj_dgesvd_mg",
+    "svdj_mg_rank_create",
+    "svdj_mg_rank_destroy",
+    "svdj_mg_rank_dgesvd",
+    "svdj_mg_rank_dgesvd_device",
+    "svdj_mg_plan",
+    "svdj_device_count",
     "svdj_num_steps",
     "svdj_schedule_step",
     "svdj_block_schedule_step",
@@ -168,6 +183,21 @@ def _load() -> C.CDLL:
     lib.svdj_dgesvd_rows_device.argtypes = [C.c_int, C.c_int, sz, sz, C.c_void_p, sz, C.c_void_p, C.c_void_p, sz, sz, sz,
                                             C.POINTER(Opts), C.POINTER(Stats), C.c_void_p, AllreduceFn, C.c_void_p]
     lib.svdj_dgesvd_rows_device.restype = C.c_int
+    ip = C.POINTER(C.c_int)
+    lib.svdj_dgesvd_mg.argtypes = [i, i, sz, sz, vp, sz, vp, vp, sz, C.POINTER(Opts), C.POINTER(Stats), i, ip]
+    lib.svdj_dgesvd_mg.restype = i
+    lib.svdj_mg_rank_create.argtypes = [C.POINTER(MgComm), sz, sz, C.POINTER(C.c_void_p)]
+    lib.svdj_mg_rank_create.restype = i
+    lib.svdj_mg_rank_destroy.argtypes = [vp]
+    lib.svdj_mg_rank_destroy.restype = i
+    lib.svdj_mg_rank_dgesvd.argtypes = [vp, i, i, sz, sz, vp, sz, vp, vp, sz, C.POINTER(Opts), C.POINTER(Stats)]
+    lib.svdj_mg_rank_dgesvd.restype = i
+    lib.svdj_mg_rank_dgesvd_device.argtypes = [vp, i, i, sz, sz, vp, sz, vp, vp, sz, C.POINTER(Opts), C.POINTER(Stats)]
+    lib.svdj_mg_rank_dgesvd_device.restype = i
+    lib.svdj_mg_plan.argtypes = [i, i, ip, ip, ip, ip, ip, ip]
+    lib.svdj_mg_plan.restype = i
+    lib.svdj_device_count.argtypes = []
+    lib.svdj_device_count.restype = i
     lib.svdj_release_workspace.argtypes = []
     lib.svdj_release_workspace.restype = i
     lib.svdj_last_error.argtypes = []
@@ -299,3 +329,32 @@ def step_device_noalloc(m, n, dA: int, lda, dV: int, ldv, rotate_v, step, tol, t
     rc = lib.svdj_step_device_noalloc(m, n, dA, lda, dV or None, ldv, int(rotate_v), step, tol, threshold_mode,
                                       d_counters or None, stream or None)
     _check(rc)
+
+
+def dgesvd_mg(jobu, jobv, m, n, A, lda, s, V, ldv, ngpus: int, devices=None, opts: Opts | None = None,
+              allow_not_converged=False) -> Stats:
+    """The reference's distributed entry point as one call on `ngpus` GPUs of this process (svdj_dgesvd_mg): host
+    arrays in and out like :func:`dgesvd`.  `devices`: CUDA ordinals of the ranks (default 0 .. ngpus-1)."""
+    st = Stats()
+    dev = None
+    if devices is not None:
+        if len(devices) != ngpus:
+            raise ValueError("one device ordinal per rank")
+        dev = (C.c_int * ngpus)(*devices)
+    rc = lib.svdj_dgesvd_mg(jobu, jobv, m, n, _host_ptr(A, "A"), lda, _host_ptr(s, "s"),
+                            None if V is None else _host_ptr(V, "V"), ldv, None if opts is None else C.byref(opts),
+                            C.byref(st), ngpus, dev)
+    _check(rc, allow_not_converged)
+    st.rc = rc
+    return st
+
+
+def mg_plan(P: int, rnd: int):
+    """(top_block, bottom_block, top_buf, bottom_buf, transfers) of the multi-GPU tournament after `rnd` moves."""
+    arr = [(C.c_int * P)() for _ in range(4)]
+    tr = (C.c_int * (8 * P))()
+    cnt = C.c_int()
+    rc = lib.svdj_mg_plan(P, rnd, arr[0], arr[1], arr[2], arr[3], tr, C.byref(cnt))
+    _check(rc)
+    return (list(arr[0]), list(arr[1]), list(arr[2]), list(arr[3]),
+            [tuple(tr[4 * k: 4 * k + 4]) for k in range(cnt.value)])

@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "svdj_common.cuh"
+#include "svdj_host.cuh"
 #include "svdj_qr.cuh"
 
 namespace svdj {
@@ -42,138 +43,7 @@ static double now_s() {
   return duration<double>(steady_clock::now().time_since_epoch()).count();
 }
 
-// Work buffers come from a small process-wide pool (per device for device memory): cudaMalloc, cudaFree and
-// cudaMallocHost are device-wide synchronising driver calls that can stall for ~100 ms behind any other driver
-// client (a monitoring query is enough), which used to land inside the solve.  A buffer returns to the pool when
-// its RAII holder dies; svdj_release_workspace() gives everything idle back to the driver.
-struct Pool {
-  struct Entry {
-    void *p;
-    size_t bytes;
-    int device;  // -1 for pinned host memory
-    bool busy;
-  };
-  std::mutex mu;
-  std::vector<Entry> entries;
-
-  void *acquire(size_t bytes, int device, cudaError_t *err) {
-    std::lock_guard<std::mutex> lock(mu);
-    Entry *best = nullptr;
-    for (auto &e : entries) {
-      if (!e.busy && e.device == device && e.bytes >= bytes && e.bytes <= 2 * bytes + 4096 &&
-          (best == nullptr || e.bytes < best->bytes))
-        best = &e;
-    }
-    if (best) {
-      best->busy = true;
-      *err = cudaSuccess;
-      return best->p;
-    }
-    void *p = nullptr;
-    *err = (device < 0) ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
-    if (*err != cudaSuccess) return nullptr;
-    entries.push_back({p, bytes, device, true});
-    return p;
-  }
-  void release(void *p) {
-    std::lock_guard<std::mutex> lock(mu);
-    for (auto &e : entries)
-      if (e.p == p) e.busy = false;
-  }
-  void trim() {
-    std::lock_guard<std::mutex> lock(mu);
-    std::vector<Entry> keep;
-    int cur = -1;
-    cudaGetDevice(&cur);
-    for (auto &e : entries) {
-      if (e.busy) {
-        keep.push_back(e);
-      } else if (e.device < 0) {
-        cudaFreeHost(e.p);
-      } else {
-        cudaSetDevice(e.device);
-        cudaFree(e.p);
-      }
-    }
-    if (cur >= 0) cudaSetDevice(cur);
-    entries.swap(keep);
-  }
-};
-static Pool g_pool;
-
-// RAII for device / pinned buffers and events so that every early return releases them
-struct DevBuf {
-  void *p = nullptr;
-  ~DevBuf() {
-    if (p) g_pool.release(p);
-  }
-  int alloc(size_t bytes) {
-    if (bytes == 0) bytes = 8;
-    int dev = 0;
-    SVDJ_CUDA_TRY(cudaGetDevice(&dev));
-    cudaError_t e;
-    p = g_pool.acquire(bytes, dev, &e);
-    if (p == nullptr) {
-      set_error("cudaMalloc(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
-      cudaGetLastError();
-      return SVDJ_ERR_ALLOC;
-    }
-    return SVDJ_OK;
-  }
-  template <class T>
-  T *as() const {
-    return static_cast<T *>(p);
-  }
-};
-
-struct PinBuf {
-  void *p = nullptr;
-  ~PinBuf() {
-    if (p) g_pool.release(p);
-  }
-  int alloc(size_t bytes) {
-    cudaError_t e;
-    p = g_pool.acquire(bytes ? bytes : 8, -1, &e);
-    if (p == nullptr) {
-      set_error("cudaMallocHost(%zu bytes) -> %s", bytes, cudaGetErrorString(e));
-      cudaGetLastError();
-      return SVDJ_ERR_ALLOC;
-    }
-    return SVDJ_OK;
-  }
-  template <class T>
-  T *as() const {
-    return static_cast<T *>(p);
-  }
-};
-
-struct Event {
-  cudaEvent_t e = nullptr;
-  ~Event() {
-    if (e) cudaEventDestroy(e);
-  }
-  int create() {
-    SVDJ_CUDA_TRY(cudaEventCreate(&e));
-    return SVDJ_OK;
-  }
-};
-
-struct DeviceGuard {
-  int prev = -1;
-  bool active = false;
-  int enter(int dev) {
-    if (dev < 0) return SVDJ_OK;
-    SVDJ_CUDA_TRY(cudaGetDevice(&prev));
-    if (prev != dev) {
-      SVDJ_CUDA_TRY(cudaSetDevice(dev));
-      active = true;
-    }
-    return SVDJ_OK;
-  }
-  ~DeviceGuard() {
-    if (active) cudaSetDevice(prev);
-  }
-};
+Pool g_pool;
 
 // Default threshold of the relative test: LAPACK dgesvj's CTOL -- sqrt(m) when singular vectors are wanted (the
 // columns must come out orthogonal to working precision: |U^T U - I| <= 10 n eps needs cosines ~ sqrt(m) eps,
@@ -745,11 +615,21 @@ void svdj_default_opts(svdj_opts *o) {
 const char *svdj_last_error(void) { return g_error; }
 
 int svdj_release_workspace(void) {
+  mg_release_team();
   g_pool.trim();
   return SVDJ_OK;
 }
 
-int svdj_version(void) { return 100; }
+int svdj_version(void) { return 200; }
+
+int svdj_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
 
 size_t svdj_num_steps(size_t n) { return n < 2 ? 0 : 2 * ((n + 1) / 2) - 1; }
 

@@ -333,6 +333,13 @@ int blk32_launch_step(const BlockArgs &a, unsigned k, double *gpart, double *wbu
 size_t blk32_gred_doubles(unsigned nb);  // all-reduce buffer of the row-sharded driver for nb column blocks
 double default_tol(size_t m, int jobu, int jobv);
 
+// One phase of a ring rank on its two resident column blocks (svdj_ring.cu; ws from svdj_ring_ws_create).
+// redirect_last: the last step's update kernel stores the blocks at dst* (null = in place) and rewrites every pair.
+int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
+               double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
+               unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
+               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches);
+
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0 = 0);
 int launch_square(double *x, size_t n, cudaStream_t st);

@@ -88,10 +88,13 @@ int svdj_ring_ws_destroy(void *ws) {
   return SVDJ_OK;
 }
 
-static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
-                      double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
-                      int inner_sweeps, unsigned long long *d_counters, void *stream, double *dstA_left,
-                      double *dstA_right, double *dstV_left, double *dstV_right, bool redirect_last) {
+}  // extern "C"
+
+namespace svdj {
+int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
+               double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
+               unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
+               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches) {
   RingWorkspace *W = static_cast<RingWorkspace *>(ws);
   if (W == nullptr) return -1;
   if (m == 0 || m != W->m) return -2;
@@ -146,16 +149,19 @@ static int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_lef
       b.V2_st = dstV_right ? dstV_right : dV_right;
       b.force_update = 1;
     }
-    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, nullptr, nullptr, nullptr)) return rc;
+    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, launches, nullptr, nullptr)) return rc;
   }
   return SVDJ_OK;
 }
+}  // namespace svdj
+
+extern "C" {
 
 int svdj_ring_phase_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
                            double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol,
                            int inner_sweeps, unsigned long long *d_counters, void *stream) {
   return ring_phase(ws, m, vrows, w, dA_left, dA_right, lda, dV_left, dV_right, ldv, rotate_v, phase, tol,
-                    inner_sweeps, d_counters, stream, nullptr, nullptr, nullptr, nullptr, false);
+                    inner_sweeps, d_counters, stream, nullptr, nullptr, nullptr, nullptr, false, nullptr);
 }
 
 int svdj_ring_phase_send_device(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right,
@@ -163,7 +169,7 @@ int svdj_ring_phase_send_device(void *ws, size_t m, size_t vrows, size_t w, doub
                                 int inner_sweeps, unsigned long long *d_counters, double *dstA_left,
                                 double *dstV_left, double *dstA_right, double *dstV_right, void *stream) {
   return ring_phase(ws, m, vrows, w, dA_left, dA_right, lda, dV_left, dV_right, ldv, 1, phase, tol, inner_sweeps,
-                    d_counters, stream, dstA_left, dstA_right, dstV_left, dstV_right, true);
+                    d_counters, stream, dstA_left, dstA_right, dstV_left, dstV_right, true, nullptr);
 }
 
 // ---- device memory that other processes can map (CUDA IPC) ------------------------------------------------

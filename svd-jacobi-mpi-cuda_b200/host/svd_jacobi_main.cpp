@@ -1,4 +1,4 @@
-// svd_jacobi <n> [--no-check] [--seed S] [--dense]
+// svd_jacobi <n> [--no-check] [--seed S] [--dense] [--gpus N]
 //
 // Driver with the reference's workflow (main.cu:1426-1676): build the n x n input (upper triangle filled
 // row by row from std::default_random_engine(1000000), main.cu:1445 and :1559-1567), time the solve
@@ -7,8 +7,9 @@
 // main.cu:1583, :1638, :1665), write reporte-dimension-<n>-time-<dd-mm-YYYY-HH-MM-SS>.txt (main.cu:1667),
 // and add one JSON line with what the reference never reported (sweeps, rotations, accuracy).
 //
-// Differences by design: no MPI_Init (one process drives the GPU), no "Test 1" on a random unseeded
-// matrix (main.cu:1461-1534), thread count is not forced to 36 (main.cu:1431).
+// Differences by design: no MPI_Init (one process drives the GPUs: --gpus N or SVDJ_NGPUS, through the in-library
+// multi-GPU driver, where the reference uses mpiexec -n P), no "Test 1" on a random unseeded matrix
+// (main.cu:1461-1534), thread count is not forced to 36 (main.cu:1431; the report's "Number of threads" line is kept).
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -17,6 +18,7 @@
 #include <fstream>
 #include <iomanip>
 #include <iostream>
+#include <omp.h>
 #include <random>
 #include <sstream>
 #include <string>
@@ -31,16 +33,18 @@ static double wall() {
 
 int main(int argc, char **argv) {
   if (argc < 2) {
-    std::fprintf(stderr, "usage: %s <n> [--no-check] [--seed S] [--dense]\n", argv[0]);
+    std::fprintf(stderr, "usage: %s <n> [--no-check] [--seed S] [--dense] [--gpus N]\n", argv[0]);
     return 2;
   }
   const std::size_t n = std::stoul(argv[1]);
   bool check = true, dense = false;
   unsigned seed = 1000000;
+  int gpus = svdj_shim::ngpus_from_env();
   for (int i = 2; i < argc; ++i) {
     if (!std::strcmp(argv[i], "--no-check")) check = false;
     else if (!std::strcmp(argv[i], "--dense")) dense = true;
     else if (!std::strcmp(argv[i], "--seed") && i + 1 < argc) seed = (unsigned)std::stoul(argv[++i]);
+    else if (!std::strcmp(argv[i], "--gpus") && i + 1 < argc) gpus = std::atoi(argv[++i]);
   }
   const std::size_t height = n, width = n;
 
@@ -60,6 +64,8 @@ int main(int argc, char **argv) {
     for (std::size_t col = dense ? 0 : row; col < n; ++col) A.elements[col * height + row] = dist(engine);
   std::copy(A.elements, A.elements + height * width, A_copy.elements);
 
+  // main.cu:1581 (omp_get_num_threads() outside a parallel region: 1 in the reference too)
+  report << "Number of threads: " << omp_get_num_threads() << '\n';
   report << "Dimensions, height: " << height << ", width: " << width << "\n";
   std::cout << "Dimensions, height: " << height << ", width: " << width << "\n";
 
@@ -69,7 +75,8 @@ int main(int argc, char **argv) {
   int rc = 0;
   try {
     // same call as main.cu:1587-1595, plus the stats the reference has no channel for
-    svdj_shim::solve(AllVec, AllVec, height, width, A.elements, height, s.elements, V.elements, width, nullptr, &st);
+    svdj_shim::solve_mg(AllVec, AllVec, height, width, A.elements, height, s.elements, V.elements, width, gpus, nullptr,
+                        &st);
   } catch (const std::exception &e) {
     std::cerr << e.what() << "\n";
     rc = 1;
@@ -105,9 +112,9 @@ int main(int argc, char **argv) {
 
   std::printf("{\"n\": %zu, \"seconds\": %.6f, \"sweeps\": %d, \"converged\": %d, \"rotations_applied\": %llu, "
               "\"pairs_tested\": %llu, \"last_offdiag\": %.3e, \"seconds_sweeps\": %.6f, \"residual_fro\": %.3e, "
-              "\"report\": \"%s\"}\n",
+              "\"gpus\": %d, \"report\": \"%s\"}\n",
               n, time, st.sweeps, st.converged, st.applied, st.tested, st.last_offdiag, st.seconds_sweeps, fro,
-              name.c_str());
+              gpus, name.c_str());
   A.free();
   V.free();
   s.free();
