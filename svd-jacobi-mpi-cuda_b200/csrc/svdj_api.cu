@@ -351,7 +351,12 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
       std::fprintf(stderr, "[svdj] sweep %2d: rotations %llu, max off-diagonal cosine %.3e (tol %.3e)\n", sweep + 1,
                    (unsigned long long)hc->applied, off, o.tol);
     }
-    if (hc->applied == 0) {
+    // Converged: a sweep that rotated nothing (the reference's rule applied to lib/JacobiMethods.cu:462-466), or --
+    // block path -- one in which no pair was seen above 2 tol.  tol = sqrt(m) eps sits AT the rounding noise of an
+    // m-term inner product, so a finished solve keeps finding a handful of pairs a hair above it (4096^2: "2
+    // rotations, max cosine 7.116e-15" against tol 7.105e-15) and would pay a whole extra sweep for them; the pairs
+    // above tol were rotated in this sweep anyway.
+    if (hc->applied == 0 || (block && o.threshold_mode == SVDJ_THRESH_REL && off <= 2.0 * o.tol)) {
       converged = true;
       break;
     }

@@ -25,6 +25,7 @@
 // torchrun) map each other's buffers through CUDA IPC (svdj_mg_rank_*).  Same code either way: the only thing a
 // communicator has to provide is an all-gather of a few hundred host bytes at set-up.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
@@ -79,7 +80,8 @@ __global__ void mg_start_kernel(u64 *ctl, u64 floor_bits, u64 stamp) {
 
 // Spins until both flags have reached `stamp`.  A peer that never arrives (it failed) must not hang this GPU for
 // ever: after timeout_ns the kernel records the failure in *err and returns; the host checks *err once per sweep.
-__global__ void mg_wait_kernel(const u64 *f0, const u64 *f1, u64 stamp, u64 *err, u64 timeout_ns) {
+// *err = (kind << 56) | (which flag << 48) | stamp: what was waited for when the time ran out
+__global__ void mg_wait_kernel(const u64 *f0, const u64 *f1, u64 stamp, u64 *err, u64 timeout_ns, int kind = 1) {
   if (*reinterpret_cast<volatile u64 *>(err) != 0) return;  // an earlier wait of this solve already gave up
   const u64 t0 = global_timer_ns();
   for (int i = 0; i < 2; ++i) {
@@ -87,7 +89,7 @@ __global__ void mg_wait_kernel(const u64 *f0, const u64 *f1, u64 stamp, u64 *err
     if (f == nullptr) continue;
     while (ld_acquire_sys(f) < stamp) {
       if (global_timer_ns() - t0 > timeout_ns) {
-        *err = stamp;
+        *err = ((u64)kind << 56) | ((u64)i << 48) | stamp;
         return;
       }
       __nanosleep(200);
@@ -117,7 +119,7 @@ __global__ void mg_collect_kernel(const u64 *mail, int P, u64 stamp, u64 *out, u
     const u64 *slot = mail + 4 * q;
     while (ld_acquire_sys(slot + 2) < stamp) {
       if (global_timer_ns() - t0 > timeout_ns) {
-        *err = stamp;
+        *err = (2ull << 56) | ((u64)q << 48) | stamp;
         out[0] = ~0ull;
         return;
       }
@@ -186,7 +188,17 @@ struct Comm {
   // Ranks in different processes own their device and need no such barrier.
   // Returns the first non-zero status among the ranks (so that one rank's failed allocation stops all of them).
   virtual int before_first_launch(int my_status) { return my_status; }
+  // Ranks that SHARE a GPU (threads of one process on one device: the one-GPU test mode).  A kernel that spins on a
+  // flag may only be launched once the work that will set the flag has been submitted: streams of one device can
+  // share a hardware queue, and a spinning kernel at its head then blocks the very kernel it is waiting for.  For
+  // such a pair the signalling rank records an event after its signal and publishes the stamp on the host; the
+  // waiting rank waits (on the host) for the publication and makes its stream wait for the event, so the spinning
+  // kernel finds its flag already set.  Ranks on different GPUs have their own queues: no-ops there.
+  virtual void set_devices(const std::vector<int> &) {}
+  virtual void publish(int kind, int dst, u64 stamp, cudaStream_t s) { (void)kind, (void)dst, (void)stamp, (void)s; }
+  virtual void await(int kind, int src, u64 stamp, cudaStream_t s) { (void)kind, (void)src, (void)stamp, (void)s; }
 };
+enum { kChanStart = 0, kChanRound = 1, kChanMail = 2, kChanSigma = 3, kChanDone = 4, kChans = 5 };
 
 struct CallbackComm : Comm {
   svdj_allgather_fn fn;
@@ -201,9 +213,47 @@ struct LocalHub {
   int size = 1, arrived = 0;
   unsigned long generation = 0;
   std::vector<unsigned char> buf;
+  // same-device ordering (Comm::publish / await): one event and one published stamp per (channel, src, dst)
+  std::vector<cudaEvent_t> ev;
+  std::unique_ptr<std::atomic<u64>[]> pub;
+  size_t slot(int kind, int src, int dst) const { return ((size_t)kind * size + src) * size + dst; }
+  void init_board(int P) {
+    size = P;
+    ev.assign((size_t)kChans * P * P, nullptr);
+    pub.reset(new std::atomic<u64>[(size_t)kChans * P * P]);
+    for (size_t i = 0; i < (size_t)kChans * P * P; ++i) pub[i].store(0);
+  }
 };
 struct LocalComm : Comm {
   LocalHub *hub = nullptr;
+  std::vector<int> devices;
+  void set_devices(const std::vector<int> &d) override {
+    devices = d;
+    for (int q = 0; q < size; ++q) {
+      if (q == rank || devices[q] != devices[rank]) continue;
+      for (int k = 0; k < kChans; ++k) {
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess) hub->ev[hub->slot(k, rank, q)] = e;
+      }
+    }
+  }
+  bool shares_device(int q) const { return q != rank && !devices.empty() && devices[q] == devices[rank]; }
+  void publish(int kind, int dst, u64 stamp, cudaStream_t s) override {
+    if (!shares_device(dst)) return;
+    const size_t i = hub->slot(kind, rank, dst);
+    if (hub->ev[i]) cudaEventRecord(hub->ev[i], s);
+    hub->pub[i].store(stamp, std::memory_order_release);
+  }
+  void await(int kind, int src, u64 stamp, cudaStream_t s) override {
+    if (!shares_device(src)) return;
+    const size_t i = hub->slot(kind, src, rank);
+    const auto t0 = std::chrono::steady_clock::now();
+    while (hub->pub[i].load(std::memory_order_acquire) < stamp) {
+      if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(60)) return;  // the device-side wait reports it
+      std::this_thread::yield();
+    }
+    if (hub->ev[i]) cudaStreamWaitEvent(s, hub->ev[i], 0);
+  }
   int before_first_launch(int my_status) override {
     std::vector<int> all((size_t)size);
     allgather(&my_status, all.data(), sizeof(int));
@@ -532,6 +582,11 @@ static int mg_create(std::unique_ptr<Comm> comm, size_t max_m, size_t max_n, MgR
       return rc != SVDJ_OK ? rc : bad;
     }
   }
+  {
+    std::vector<int> devs((size_t)P);
+    for (int q = 0; q < P; ++q) devs[q] = (all[q].pid == mine.pid) ? all[q].device : -1 - q;  // other processes: never shared
+    R->comm->set_devices(devs);
+  }
   int map_rc = mg_map_peers(R, all);
   std::vector<int> map_all((size_t)P);
   if (R->comm->allgather(&map_rc, map_all.data(), sizeof(int)) != 0) map_rc = map_rc ? map_rc : SVDJ_ERR_CUDA;
@@ -621,6 +676,7 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
     }
     for (int q = 0; q < P; ++q) {
       mg_start_kernel<<<1, 1, 0, s>>>(R->peer_ctl[q], fl_bits, epoch);
+      R->comm->publish(kChanStart, q, epoch, s);
       ++launches;
     }
     SVDJ_CUDA_TRY(cudaGetLastError());
@@ -633,7 +689,8 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
                                                  (unsigned)((size_t)(P + me) * w));
     launches += 2;
   }
-  mg_wait_kernel<<<1, 1, 0, s>>>(R->ctl + 32, nullptr, epoch, err, kTimeoutNs);
+  R->comm->await(kChanStart, 0, epoch, s);
+  mg_wait_kernel<<<1, 1, 0, s>>>(R->ctl + 32, nullptr, epoch, err, kTimeoutNs, 3);
   ++launches;
   SVDJ_CUDA_TRY(cudaGetLastError());
   // the floor arrives with the start flag
@@ -648,6 +705,7 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, s));
   const int rounds = 2 * P - 1;
   const bool rotate_v = want_v;
+  const bool trace = std::getenv("SVDJ_MG_TRACE") != nullptr;
   bool converged = false;
   std::vector<Role> next;
   std::vector<Transfer> tr;
@@ -676,23 +734,36 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
           if (t.dst_rank == me && nw < 2) wt[nw++] = R->ctl + (t.src_rank < me ? 0 : 16);
         }
         mg_signal_kernel<<<1, 1, 0, s>>>(sig[0], sig[1], stamp);
+        for (const Transfer &t : tr)
+          if (t.src_rank == me) R->comm->publish(kChanRound, t.dst_rank, stamp, s);
+        for (const Transfer &t : tr)
+          if (t.dst_rank == me) R->comm->await(kChanRound, t.src_rank, stamp, s);
         mg_wait_kernel<<<1, 1, 0, s>>>(wt[0], wt[1], stamp, err, kTimeoutNs);
         launches += 2;
       }
       roles.swap(next);
+      if (trace) std::fprintf(stderr, "[svdj mg] rank %d queued sweep %d round %d (stamp %llu)\n", me, sweep + 1, rd,
+                              (unsigned long long)R->round_stamp);
     }
     // convergence: every rank posts its counters to every rank, all take the same decision
     const u64 sstamp = ++R->sweep_stamp;
     const int par = (int)(sstamp & 1);
     mg_post_counters_kernel<<<1, 32, 0, s>>>(R->d_counters, R->d_mail_ptrs[par], me, P, sstamp);
+    for (int q = 0; q < P; ++q) R->comm->publish(kChanMail, q, sstamp, s);
+    for (int q = 0; q < P; ++q) R->comm->await(kChanMail, q, sstamp, s);
     mg_collect_kernel<<<1, 1, 0, s>>>(R->ctl + R->mail_off(par), P, sstamp, R->d_out, err, kTimeoutNs);
     launches += 2;
     SVDJ_CUDA_TRY(cudaMemcpyAsync(R->h_out, R->d_out, 2 * sizeof(u64), cudaMemcpyDeviceToHost, s));
     SVDJ_CUDA_TRY(cudaStreamSynchronize(s));
     if (R->h_out[0] == ~0ull) {
+      u64 code = 0;
+      cudaMemcpyAsync(&code, err, sizeof(u64), cudaMemcpyDeviceToHost, s);
+      cudaStreamSynchronize(s);
       cudaMemsetAsync(err, 0, sizeof(u64), s);
-      set_error("svdj_mg: rank %d waited more than %llu s for its peers in sweep %d (a peer failed or never called)",
-                me, (unsigned long long)(kTimeoutNs / 1000000000ull), sweep + 1);
+      set_error("svdj_mg: rank %d waited more than %llu s for its peers in sweep %d (a peer failed or never called; "
+                "wait kind %llu, index %llu, stamp %llu; 1 = round flag, 2 = sweep mailbox, 3 = start)",
+                me, (unsigned long long)(kTimeoutNs / 1000000000ull), sweep + 1, code >> 56, (code >> 48) & 0xffull,
+                code & 0xffffffffffffull);
       return SVDJ_ERR_CUDA;
     }
     st.sweeps = sweep + 1;
@@ -701,10 +772,11 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
     std::memcpy(&off, &R->h_out[1], sizeof(double));
     st.last_offdiag = off;
     st.tested += (unsigned long long)npad * (npad - 1) / 2;
+    if (trace) std::fprintf(stderr, "[svdj mg] rank %d sweep %d done\n", me, sweep + 1);
     if (std::getenv("SVDJ_TRACE") != nullptr && root)
       std::fprintf(stderr, "[svdj mg] sweep %2d: rotations %llu, max off-diagonal cosine %.3e\n", sweep + 1,
                    (unsigned long long)R->h_out[0], off);
-    if (R->h_out[0] == 0) {
+    if (R->h_out[0] == 0 || off <= 2.0 * o.tol) {  // as in the single-GPU driver (svdj_api.cu)
       converged = true;
       break;
     }
@@ -719,6 +791,7 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   launches += want_u ? 4 : 2;
   double *root_mail = reinterpret_cast<double *>(R->peer_ctl[0] + R->sigma_off()) + (size_t)me * (2 * R->w_max + 2);
   mg_post_sigma_kernel<<<1, 256, 0, s>>>(R->d_sigma, (unsigned)(2 * w), root_mail, epoch);
+  R->comm->publish(kChanSigma, 0, epoch, s);
   ++launches;
   SVDJ_CUDA_TRY(cudaGetLastError());
 
@@ -727,8 +800,9 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
     const size_t slot = 2 * R->w_max + 2;
     double *mail = reinterpret_cast<double *>(R->ctl + R->sigma_off());
     for (int q = 0; q < P; ++q) {
+      R->comm->await(kChanSigma, q, epoch, s);
       mg_wait_kernel<<<1, 1, 0, s>>>(reinterpret_cast<const u64 *>(mail + (size_t)q * slot + 2 * w), nullptr, epoch, err,
-                                     kTimeoutNs);
+                                     kTimeoutNs, 4);
       ++launches;
     }
     std::vector<double> hs((size_t)P * slot);
@@ -784,13 +858,15 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
     }
     for (int q = 0; q < P; ++q) {
       mg_signal_kernel<<<1, 1, 0, s>>>(R->peer_ctl[q] + 48, nullptr, epoch);
+      R->comm->publish(kChanDone, q, epoch, s);
       ++launches;
     }
     SVDJ_CUDA_TRY(cudaGetLastError());
     SVDJ_CUDA_TRY(cudaStreamSynchronize(s));  // src / sig must outlive their copies
   }
   // nobody reuses its buffers before the root has read them
-  mg_wait_kernel<<<1, 1, 0, s>>>(R->ctl + 48, nullptr, epoch, err, kTimeoutNs);
+  R->comm->await(kChanDone, 0, epoch, s);
+  mg_wait_kernel<<<1, 1, 0, s>>>(R->ctl + 48, nullptr, epoch, err, kTimeoutNs, 5);
   ++launches;
   u64 herr = 0;
   SVDJ_CUDA_TRY(cudaMemcpyAsync(&herr, err, sizeof(u64), cudaMemcpyDeviceToHost, s));
@@ -1014,6 +1090,11 @@ static void team_destroy(LocalTeam *t) {
   if (!t) return;
   for (MgRank *r : t->ranks) mg_destroy(r);
   t->ranks.clear();
+  for (cudaEvent_t &e : t->hub.ev) {
+    if (e) cudaEventDestroy(e);
+    e = nullptr;
+  }
+  cudaGetLastError();
 }
 
 void mg_release_team() {
@@ -1059,7 +1140,7 @@ extern "C" int svdj_dgesvd_mg(int jobu, int jobv, size_t m, size_t n, double *A,
     g_team->devices = devs;
     g_team->max_m = m;
     g_team->max_n = n;
-    g_team->hub.size = ngpus;
+    g_team->hub.init_board(ngpus);
     g_team->ranks.assign((size_t)ngpus, nullptr);
     std::vector<int> rcs((size_t)ngpus, 0);
     std::vector<std::string> errs((size_t)ngpus);
@@ -1111,11 +1192,29 @@ extern "C" int svdj_dgesvd_mg(int jobu, int jobv, size_t m, size_t n, double *A,
     *stats = sts[0];
     for (int r = 1; r < ngpus; ++r) stats->launches += sts[r].launches;
   }
+  // report the cause, not its echo: a rank that timed out waiting is usually the victim of another rank's failure
+  int bad = -1;
   for (int r = 0; r < ngpus; ++r) {
-    if (rcs[r] != SVDJ_OK && rcs[r] != SVDJ_NOT_CONVERGED) {
-      set_error("svdj_dgesvd_mg: rank %d failed: %s", r, errs[r].c_str());
-      return rcs[r];
+    if (rcs[r] == SVDJ_OK || rcs[r] == SVDJ_NOT_CONVERGED) continue;
+    const bool echo = errs[r].find("waited more than") != std::string::npos ||
+                      errs[r].find("another rank failed") != std::string::npos;
+    if (bad < 0 || !echo) {
+      const bool bad_is_echo = bad >= 0 && (errs[bad].find("waited more than") != std::string::npos ||
+                                            errs[bad].find("another rank failed") != std::string::npos);
+      if (bad < 0 || bad_is_echo) bad = r;
     }
   }
+  if (bad >= 0) {
+    std::string all;
+    for (int r = 0; r < ngpus; ++r)
+      if (rcs[r] != SVDJ_OK && rcs[r] != SVDJ_NOT_CONVERGED) all += " [rank " + std::to_string(r) + ": " + errs[r] + "]";
+    set_error("svdj_dgesvd_mg: rank %d failed (status %d):%s", bad, rcs[bad], all.c_str());
+    return rcs[bad];
+  }
+  for (int r = 1; r < ngpus; ++r)
+    if (rcs[r] != rcs[0]) {
+      set_error("svdj_dgesvd_mg: the ranks disagree on convergence (rank 0: %d, rank %d: %d)", rcs[0], r, rcs[r]);
+      return SVDJ_ERR_CUDA;
+    }
   return rcs[0];
 }

@@ -395,7 +395,9 @@ class RingSolver:
             last_off = float(host[1:2].view(torch.float64)[0])
             applied_total += applied
             sweeps = sweep + 1
-            if applied == 0 or (self.early_stop and quadratic_stop(applied, last_off, self.tol)):
+            # (0 < last_off <= 2 tol: nothing seen above the rounding noise of the inner products, csrc/svdj_api.cu)
+            if applied == 0 or 0.0 < last_off <= 2.0 * self.tol or (
+                    self.early_stop and quadratic_stop(applied, last_off, self.tol)):
                 converged = True
                 break
         return {"sweeps": sweeps, "converged": converged, "applied": applied_total, "last_offdiag": last_off,

@@ -279,7 +279,7 @@ def test_quadratic_stop_saves_the_confirming_sweep_only(svdj, monkeypatch):
     A2, s2, V2, st2 = _solve(svdj, A0, svdj.VARIANT_BLOCK)
     assert st1.converged == 1 and st2.converged == 1
     assert st2.sweeps - st1.sweeps in (0, 1)
-    assert st2.last_offdiag <= m ** 0.5 * 2.0 ** -53 * (1 + 1e-9)     # the confirming sweep saw nothing above tol
+    assert st2.last_offdiag <= 2 * m ** 0.5 * 2.0 ** -53              # the last sweep saw nothing above 2 tol
     assert H.sigma_error_normwise(s1, s2) <= 1e-14
     q = H.svd_quality(A0, A1, s1, V1)
     bound = 10 * n * H.EPS
