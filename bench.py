@@ -36,10 +36,19 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "svd_time_to_solution"
 UNIT = "s"
-# sweeps the reference's algorithm (its ordering, relative test tol = m*2^-53) needs on the bench input;
-# 512/1024: the oracle's own count; 4096: the CUDA level-1 path (same ordering, same counts as the oracle wherever
-# both were run); 2048/8192/16384 extrapolated at +2 sweeps per doubling of n.
-SWEEPS_TO_CONVERGE = {512: 14, 1024: 15, 2048: 17, 4096: 19, 8192: 21, 16384: 23}
+
+
+def sweeps_to_converge(n, fallback):
+    """Sweeps the reference's algorithm (its ordering, the relative test with tol = sqrt(m) 2^-53) needs on the bench
+    input of size n: read from profiles/sweeps_to_converge.json, which tools/record_sweeps.py writes from runs of the
+    oracle (n <= 1024, host) and of the CUDA level-1 path (same ordering; same counts as the oracle wherever both
+    ran).  Sizes that were not recorded fall back to the count the measured solve itself needed."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "sweeps_to_converge.json")))
+        return int(rec["sweeps"][str(n)])
+    except Exception:
+        return int(fallback)
+
 
 
 def peaks():
@@ -117,7 +126,7 @@ def cpu_baseline_port(A0, sweeps_needed, budget_s=15.0):
     A = A0.copy(order="F")
     V = np.asfortranarray(np.eye(n))
     steps = H.oracle_lib().oracle_num_steps(n)
-    o = H.OracleOpts(H.ORACLE_REL, m * 2.0 ** -53, 1, 0, cores, 0)
+    o = H.OracleOpts(H.ORACLE_REL, m ** 0.5 * 2.0 ** -53, 1, 0, cores, 0)
     st = H.OracleStats()
     t0 = time.perf_counter()
     done = 0
@@ -149,7 +158,7 @@ def run_reference(args):
         return 0
     n = args.n
     cores = os.cpu_count() or 1
-    sweeps_needed = SWEEPS_TO_CONVERGE.get(n, 15)
+    sweeps_needed = sweeps_to_converge(n, 19)
     A0 = H.uniform_matrix(n, n, seed=n)
     lib = H.ref_cpu_lib()
     pairs = n * (n - 1) // 2
@@ -205,109 +214,245 @@ def run_reference(args):
     return 0
 
 
-def run_ring(args, svdj, world, rank, local_rank):
-    """N > 1: the same n x n solve spread over N GPUs (strong scaling): 2N column blocks on a ring, NCCL send/recv
-    between rounds, one all-reduce per sweep (svd-jacobi-mpi-cuda_b200/ring.py)."""
+def fp64_peak_this_run():
+    """The FP64 ceilings of THIS box, measured in this run (MEASURED_PEAKS.json has no FP64 figure): cuBLAS DGEMM
+    8192^3 through torch.matmul (best of 5) and, when tools/fp64_peak is built, the DMMA issue rate of
+    mma.sync.m8n8k4.f64.  Returns (dict, larger value in TFLOP/s)."""
     import torch
-    import torch.distributed as dist
+
+    out = {}
+    n = 8192
+    a = torch.rand(n, n, dtype=torch.float64, device="cuda")
+    b = torch.rand(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    torch.cuda.synchronize()
+    best = 1e9
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e-3)
+    out["cublas_dgemm_8192_tflops"] = 2.0 * n ** 3 / best / 1e12
+    del a, b
+    exe = os.path.join(ROOT, "tools", "fp64_peak")
+    if os.path.exists(exe):
+        try:
+            txt = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120).stdout
+            for ln in txt.splitlines():
+                if "m8n8k4" in ln and "TFLOP" in ln:
+                    for tok in ln.replace(",", " ").split():
+                        try:
+                            v = float(tok)
+                        except ValueError:
+                            continue
+                        if 5.0 < v < 200.0:
+                            out["dmma_m8n8k4_tflops"] = v
+                    break
+        except Exception as exc:  # the microbenchmark is optional evidence
+            out["dmma_note"] = f"tools/fp64_peak failed: {exc}"
+    vals = [v for k, v in out.items() if k.endswith("_tflops")]
+    return out, max(vals)
+
+
+def lapack_sigma(A0_colmajor_T, n):
+    """Singular values of the bench input from an independent solver, outside every timed region: host LAPACK
+    (numpy, as the tests use) up to n = 4096, cuSOLVER's gesvd through torch above (minutes on the host otherwise)."""
+    import torch
+
+    if n <= 4096:
+        return np.linalg.svd(A0_colmajor_T.cpu().numpy().T, compute_uv=False), "numpy.linalg.svd (host LAPACK)"
+    return torch.linalg.svdvals(A0_colmajor_T.T).cpu().numpy(), "torch.linalg.svdvals (cuSOLVER gesvd)"
+
+
+def accuracy_block(A0d, Ud, Sd, Vd, n, sigma_ref, ref_name):
+    """BASELINE.json's four bounds on device tensors (U m x n, V n x n as column-major views)."""
+    import torch
+
+    eye = torch.eye(n, dtype=torch.float64, device=A0d.device)
+    s_sorted = np.sort(Sd.cpu().numpy())[::-1]
+    ref = np.sort(np.asarray(sigma_ref))[::-1]
+    acc = {"orth_u": float((Ud.T @ Ud - eye).abs().max()), "orth_v": float((Vd.T @ Vd - eye).abs().max()),
+           "resid": float(torch.linalg.norm(A0d - (Ud * Sd) @ Vd.T) / torch.linalg.norm(A0d)),
+           "bound_10_n_eps": 10 * n * 2.0 ** -52,
+           "sigma_err_vs_lapack": float(np.abs(s_sorted - ref).max() / ref[0]), "sigma_bound": 1e-12,
+           "sigma_reference": ref_name}
+    acc["ok"] = bool(acc["orth_u"] <= acc["bound_10_n_eps"] and acc["orth_v"] <= acc["bound_10_n_eps"]
+                     and acc["resid"] <= acc["bound_10_n_eps"] and acc["sigma_err_vs_lapack"] <= 1e-12)
+    return acc
+
+
+def bench_input(args, dev):
+    """(A0 as an (n, m) device tensor = the column-major bytes of the m x n matrix, workload text, sigma or None)."""
+    import torch
 
     import helpers as H
 
-    ring = importlib.import_module("svd-jacobi-mpi-cuda_b200.ring")
+    n = m = args.n
+    if args.graded:
+        g = torch.Generator(device=dev)
+        g.manual_seed(1234)
+        Q1, _ = torch.linalg.qr(torch.randn(n, n, dtype=torch.float64, device=dev, generator=g))
+        Q2, _ = torch.linalg.qr(torch.randn(n, n, dtype=torch.float64, device=dev, generator=g))
+        sig = torch.logspace(0, -12, n, dtype=torch.float64, device=dev)
+        A0 = ((Q1 * sig) @ Q2.T).T.contiguous()
+        return A0, f"{m}x{n} prescribed geometric spectrum cond 1e12 (Haar U, V) FP64, full SVD (U, S, V) to convergence", sig.cpu().numpy()
+    A0 = torch.from_numpy(np.ascontiguousarray(H.uniform_matrix(m, n, seed=n).T)).to(dev)
+    return A0, f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence", None
+
+
+def run_mg(args, svdj, world, rank, local_rank):
+    """N > 1: the same m x n solve on N GPUs (strong scaling) through the in-library C++ driver (csrc/svdj_mg.cu,
+    one rank per process): 2N column blocks on a ring, the block move fused into the update kernel (peer stores over
+    NVLink through CUDA IPC mappings), rounds ordered by flags in peer memory.  The matrix starts and ends on rank 0
+    -- the reference's contract (main.cu:1455, 1587) -- so scatter and gather are inside both timed regions."""
+    import torch
+    import torch.distributed as dist
+
+    mgmod = importlib.import_module("svd-jacobi-mpi-cuda_b200.mg")
     n = m = args.n
     dev = torch.device("cuda", local_rank)
-    solver = ring.RingSolver(m, n, dev, exchange=args.exchange)
-    w = solver.w
-
-    # every rank generates its own columns (counter-based generator: same matrix as the 1-GPU run)
-    init = {}
-    for blk in (solver.top, solver.bottom):
-        init[blk.block_id * w] = torch.from_numpy(H.uniform_columns(m, n, n, blk.block_id * w, w)).to(dev)
+    solver = mgmod.MgRank(m, n, device=dev)
+    opts = svdj.default_opts(precondition=max(args.precondition, 0))
+    root = rank == 0
+    if root:
+        dA0, workload, sigma_true = bench_input(args, dev)
+        dA = torch.empty_like(dA0)
+        ds = torch.zeros(n, dtype=torch.float64, device=dev)
+        dV = torch.empty(n, n, dtype=torch.float64, device=dev)
 
     def barrier():
         dist.barrier()
         torch.cuda.synchronize()
 
     def one_solve():
-        solver.fill_local(lambda c0, cnt: init[c0])
-        st = solver.solve()
-        sigma, order = solver.finalize()
-        return st, sigma, order
+        if root:
+            dA.copy_(dA0)
+            torch.cuda.synchronize()
+            return solver.dgesvd_device(svdj.AllVec, svdj.AllVec, m, n, dA.data_ptr(), m, ds.data_ptr(), dV.data_ptr(), n, opts)
+        return solver.dgesvd_device(svdj.AllVec, svdj.AllVec, m, n, opts=opts)
 
     for _ in range(args.warmup):
         one_solve()
     barrier()
     sampler = ClockSampler(local_rank)
-    if rank == 0:
+    if root:
         sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    solver.exchanged_bytes = 0
-    solver.backend.launches = 0
+    stats = []
     ev0.record()
     for _ in range(args.steps):
-        st, sigma, order = one_solve()
+        stats.append(one_solve())   # returns with this rank's stream drained
     ev1.record()
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if root else None
     t = torch.tensor([ev0.elapsed_time(ev1) * 1e-3], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     per_step_s = float(t.item()) / args.steps
-    sent_per_solve = solver.exchanged_bytes / args.steps
-    launches = torch.tensor([solver.backend.launches], dtype=torch.int64, device=dev)
+    launches = torch.tensor([sum(int(s_.launches) for s_ in stats)], dtype=torch.int64, device=dev)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
 
-    # e2e: the matrix starts in rank 0's pinned host memory and U, s, V end there (the reference's contract: only
-    # the root holds A, s, V -- main.cu:1455, 1548-1556)
-    hA0 = torch.from_numpy(np.ascontiguousarray(H.uniform_matrix(m, n, seed=n).T)).pin_memory() if rank == 0 else None
-    # results land in pinned host buffers the caller owns (as the single-GPU entry point's do); pageable
-    # destinations allocated inside the timed region cost ~0.1 s of page faults and staging per solve
-    if rank == 0:
-        hU = torch.empty(n, m, dtype=torch.float64).pin_memory()
+    # e2e: A starts in rank 0's pinned host memory and U, s, V end there
+    if root:
+        hA0 = dA0.cpu().pin_memory()
+        hA = torch.empty_like(hA0).pin_memory()
+        hs = torch.zeros(n, dtype=torch.float64).pin_memory()
         hV = torch.empty(n, n, dtype=torch.float64).pin_memory()
-        hs = torch.empty(n, dtype=torch.float64).pin_memory()
     e2e = []
     for it in range(1 + args.steps):
+        if root:
+            hA.copy_(hA0)
         barrier()
         t0 = time.perf_counter()
-        solver.scatter_from_root(hA0.to(dev, non_blocking=True) if rank == 0 else None)
-        st, sigma, order = solver.solve(), None, None
-        sigma, order = solver.finalize()
-        U, V = solver.gather_to_root(order)
-        if rank == 0:
-            hU.copy_(U, non_blocking=True)
-            hV.copy_(V, non_blocking=True)
-            hs.copy_(sigma, non_blocking=True)
-            torch.cuda.synchronize()
+        if root:
+            solver.dgesvd(svdj.AllVec, svdj.AllVec, m, n, hA.data_ptr(), m, hs.data_ptr(), hV.data_ptr(), n, opts)
+        else:
+            solver.dgesvd(svdj.AllVec, svdj.AllVec, m, n, opts=opts)
         barrier()
         if it > 0:
             e2e.append(time.perf_counter() - t0)
-    e2e_s = float(np.mean(e2e))
+    e2e_t = torch.tensor([float(np.mean(e2e))], dtype=torch.float64, device=dev)
+    dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_t.item())
 
-    if rank == 0:
-        Ud, Vd, Sd = hU.to(dev).T, hV.to(dev).T, hs.to(dev)
-        A0d = hA0.to(dev).T
-        eye = torch.eye(n, dtype=torch.float64, device=dev)
-        acc = {"orth_u": float((Ud.T @ Ud - eye).abs().max()), "orth_v": float((Vd.T @ Vd - eye).abs().max()),
-               "resid": float(torch.linalg.norm(A0d - (Ud * Sd) @ Vd.T) / torch.linalg.norm(A0d)),
-               "bound_10_n_eps": 10 * n * 2.0 ** -52}
+    rc = 0
+    if root:
+        last = stats[-1]
+        sigma_ref, ref_name = (sigma_true, "prescribed spectrum") if sigma_true is not None else lapack_sigma(dA0, n)
+        acc = accuracy_block(dA0.T, hA.to(dev).T, hs.to(dev), hV.to(dev).T, n, sigma_ref, ref_name)
+        # dominant kernel on rank 0: the 64-column update kernel, probed every 8th step inside the library
+        width = last.reserved or 32
+        d = 2 * width
+        pl = sum(s_.step_kernel_launches for s_ in stats)
+        pp = sum(s_.probe_block_pairs for s_ in stats)
+        k_ms = float(np.mean([s_.step_kernel_ms for s_ in stats]))
+        npad = -(-n // (64 * world)) * 64 * world
+        flops_per_launch = pp * 2.0 * (m + npad) * d * d / max(pl, 1)
+        tfs = flops_per_launch / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
+        peaks64, peak64 = fp64_peak_this_run()
         line = {
             "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence",
-                       "variant": "block", "tol": "m*2^-53 relative",
+            "config": {"workload": workload, "variant": "block", "block_width": int(width),
+                       "tol": "sqrt(m)*2^-53 relative (LAPACK dgesvj)", "precondition": int(last.precondition),
                        "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20),
-                       "parallelism": f"{2 * world} column blocks of {w} columns on a ring of {world} GPUs "
-                                      + ("(blocks stored into the neighbours' buffers by the update kernel over NVLink peer mappings, 1 all-reduce per sweep)" if args.exchange == "fused" else "(NCCL send/recv between rounds, 1 all-reduce per sweep)")},
-            "sweeps": st["sweeps"], "rotations_applied": st["applied"],
-            "ring": {"bytes_sent_per_rank_per_solve": sent_per_solve, "rounds_per_sweep": 2 * world - 1, "exchange": args.exchange},
-            "roofline": None, "cpu_baseline": None,
+                       "parallelism": f"{2 * world} column blocks of {npad // (2 * world)} columns on a ring of {world} GPUs; "
+                                      "C++ driver inside libsvdj (svdj_mg_rank_*): blocks stored into the neighbours' "
+                                      "buffers by the update kernel over NVLink (CUDA IPC mappings), rounds ordered by "
+                                      "flags in peer memory, convergence through peer mailboxes; matrix on rank 0 in and out"},
+            "sweeps": last.sweeps, "rotations_applied": int(last.applied),
+            "seconds_sweeps": float(np.mean([s_.seconds_sweeps for s_ in stats])),
+            "seconds_precond": float(np.mean([s_.seconds_precond for s_ in stats])),
+            "roofline": {"bound": "tensor", "achieved": tfs, "peak": peak64, "unit": "TFLOP/s", "frac": tfs / peak64,
+                         "traffic": None,
+                         "traffic_note": "no ncu capture at N > 1 (ncu is single-GPU here); the N = 1 capture is profiles/r2_k3_full.md",
+                         "peak_measured_this_run": peaks64,
+                         "peak_source": "larger of cuBLAS DGEMM 8192^3 and tools/fp64_peak (DMMA m8n8k4), both measured in this run on rank 0",
+                         "kernel": "blk32_update_kernel on rank 0 (X<-XW, Y<-YW for 64-column block pairs; last step of a round stores into the neighbour GPU)",
+                         "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3, "launches_probed": int(pl)},
+            "cpu_baseline": None,
             "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
                     "d2h_bytes_per_step": (m * n + n * n + n) * 8},
             "gpu_launches": int(launches.item()), "clocks": clocks, "accuracy": acc,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
+        if not acc["ok"] or any(s_.converged != 1 for s_ in stats):
+            print("bench.py: accuracy bound violated or not converged", file=sys.stderr)
+            rc = 3
+    solver.close()
     dist.destroy_process_group()
+    return rc
+
+
+def run_cusolver(args):
+    """--impl cusolver: NVIDIA's own one-sided Jacobi (cusolverDnDgesvdj through torch.linalg.svd) on the bench
+    input, as a yardstick line for profiles/ -- never on the product path."""
+    import torch
+
+    dev = torch.device("cuda", 0)
+    A0, workload, sigma_true = bench_input(args, dev)
+    n = args.n
+    A = A0.T.contiguous()
+    times = []
+    for it in range(args.warmup + args.steps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        U, S, Vh = torch.linalg.svd(A, full_matrices=False, driver="gesvdj")
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= args.warmup:
+            times.append(e0.elapsed_time(e1) * 1e-3)
+    eye = torch.eye(n, dtype=torch.float64, device=dev)
+    line = {"impl": "cusolver", "metric": METRIC, "value": float(np.mean(times)), "unit": UNIT, "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": False, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload, "solver": "cusolverDnDgesvdj via torch.linalg.svd(driver='gesvdj'), library defaults"},
+            "accuracy": {"orth_u": float((U.T @ U - eye).abs().max()), "orth_v": float((Vh @ Vh.T - eye).abs().max()),
+                         "resid": float(torch.linalg.norm(A - (U * S) @ Vh) / torch.linalg.norm(A)),
+                         "bound_10_n_eps": 10 * n * 2.0 ** -52}}
+    print(json.dumps(line))
     return 0
 
 
@@ -387,6 +532,7 @@ def run_rows(args, svdj, world, rank, local_rank):
             e2e.append(time.perf_counter() - t0)
     e2e_s = float(np.mean(e2e))
 
+    rc_rows = 0
     # accuracy from the row slices: U^T U and V^T V are sums over the ranks; the residual needs the whole (small) V
     U, V, sg = solver.U_local.T, solver.V_local.T, solver.sigma        # (m_local, n), (v_local, n)
     utu, vtv = U.T @ U, V.T @ V
@@ -399,29 +545,43 @@ def run_rows(args, svdj, world, rank, local_rank):
     res2 = torch.stack([torch.linalg.norm(A_rows.T - (U * sg) @ Vfull.T) ** 2, torch.linalg.norm(A_rows) ** 2])
     if world > 1:
         dist.all_reduce(res2)
+    gram = A_rows @ A_rows.T
+    if world > 1:
+        dist.all_reduce(gram)
     if rank == 0:
         eye = torch.eye(n, dtype=torch.float64, device=dev)
         acc = {"orth_u": float((utu - eye).abs().max()), "orth_v": float((vtv - eye).abs().max()),
-               "resid": float(torch.sqrt(res2[0] / res2[1])), "bound_10_m_eps": 10 * m * 2.0 ** -52}
+               "resid": float(torch.sqrt(res2[0] / res2[1])), "bound_10_n_eps": 10 * n * 2.0 ** -52}
+        # sigma against an independent solver: the singular values of A are the square roots of the eigenvalues of
+        # the n x n Gram matrix; for this well-conditioned N(0,1) input that route is accurate to ~cond^2 eps
+        ref = torch.sqrt(torch.linalg.eigvalsh(gram).clamp_min(0)).flip(0)
+        acc["sigma_err_vs_lapack"] = float((sg - ref).abs().max() / ref[0])
+        acc["sigma_reference"] = "sqrt(eigvalsh(A^T A)) (LAPACK dsyevd through torch), valid to ~cond^2 eps"
+        acc["sigma_bound"] = 1e-12
+        acc["ok"] = bool(max(acc["orth_u"], acc["orth_v"], acc["resid"]) <= acc["bound_10_n_eps"]
+                         and acc["sigma_err_vs_lapack"] <= 1e-12)
         launches = sum(s_.step_kernel_launches for s_ in stats)
         pairs_upd = sum(s_.probe_block_pairs for s_ in stats)
         k_ms = float(np.mean([s_.step_kernel_ms for s_ in stats]))
         flops_per_launch = pairs_upd * 2.0 * (ml + solver.v_local) * 64 * 64 / max(launches, 1)
         tfs = flops_per_launch / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
+        del gram, utu, vtv
+        peaks64, peak64 = fp64_peak_this_run()
         line = {
             "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"{m}x{n} dense N(0,1) FP64, full SVD (U, S, V) to convergence",
-                       "variant": "block", "block_width": 32, "tol": "m*2^-53 relative",
+                       "variant": "block", "block_width": 32, "tol": "sqrt(m)*2^-53 relative (LAPACK dgesvj)",
                        "l2": "inputs_larger_than_l2 (A = %d MiB)" % (m * n * 8 >> 20),
                        "parallelism": f"rows sharded over {world} GPU(s): {ml} rows of A and {solver.v_local} rows of V "
                                       "per rank, one all-reduce of the block pairs' Gram matrices per step"},
             "sweeps": st.sweeps, "rotations_applied": int(st.applied),
             "rows": {"allreduce_calls_per_solve": ar_calls, "allreduce_bytes_per_solve": ar_bytes},
-            "roofline": {"bound": "tensor", "achieved": tfs, "peak": 36.9, "unit": "TFLOP/s", "frac": tfs / 36.9,
+            "roofline": {"bound": "tensor", "achieved": tfs, "peak": peak64, "unit": "TFLOP/s", "frac": tfs / peak64,
                          "traffic": None, "kernel": "blk32_update_kernel on rank 0's rows",
-                         "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md",
+                         "peak_measured_this_run": peaks64,
+                         "peak_source": "larger of cuBLAS DGEMM 8192^3 and tools/fp64_peak (DMMA m8n8k4), measured in this run",
                          "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
                          "launches_probed": int(launches)},
             "cpu_baseline": None,
@@ -429,10 +589,13 @@ def run_rows(args, svdj, world, rank, local_rank):
                     "d2h_bytes_per_step": (m * n + n * n + n) * 8},
             "gpu_launches": int(sum(s_.launches for s_ in stats)) * world, "clocks": clocks, "accuracy": acc,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
+        if not acc["ok"]:
+            print("bench.py: accuracy bound violated", file=sys.stderr)
+            rc_rows = 3
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return rc_rows
 
 
 def run_svdj(args):
@@ -455,15 +618,15 @@ def run_svdj(args):
             raise SystemExit("--rows M is the tall-skinny workload: M >= 8 * --size")
         return run_rows(args, svdj, world, rank, local_rank)
     if world > 1:
-        return run_ring(args, svdj, world, rank, local_rank)
+        return run_mg(args, svdj, world, rank, local_rank)
 
     n = m = args.n
-    A0 = H.uniform_matrix(m, n, seed=n)
-    dA0 = torch.from_numpy(np.ascontiguousarray(A0.T)).cuda()  # column-major bytes
+    dA0, workload, sigma_true = bench_input(args, torch.device("cuda", local_rank))  # (n, m): column-major bytes
+    A0 = None if args.graded else H.uniform_matrix(m, n, seed=n)
     dA = torch.empty_like(dA0)
     ds = torch.zeros(n, dtype=torch.float64, device="cuda")
     dV = torch.empty(n, n, dtype=torch.float64, device="cuda")
-    opts = svdj.default_opts(variant=args.variant)
+    opts = svdj.default_opts(variant=args.variant, precondition=args.precondition)
     stream = torch.cuda.current_stream().cuda_stream
 
     def barrier():
@@ -515,16 +678,17 @@ def run_svdj(args):
         flops_per_launch = pairs_upd * 2.0 * (m + n) * d * d / max(launches, 1)
         gbs = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
         tfs = flops_per_launch / (k_ms * 1e-3) / 1e12 if k_ms > 0 else 0.0
-        dmma_peak = 36.9  # TFLOP/s, mma.sync.m8n8k4.f64 issue peak measured on this pool (profiles/r1_fp64_peaks.md)
-        full = (m, n) == (4096, 4096)
+        # FP64 ceiling measured in THIS run (MEASURED_PEAKS.json has none): cuBLAS DGEMM and the DMMA issue rate
+        peaks64, dmma_peak = fp64_peak_this_run()
         if width == 32:
             # 0.31 * 32 = 10 flop/B against a ridge of 36.9 TF / 6.45 TB/s = 5.7: the FP64 tensor pipe bounds it
             roofline = {"bound": "tensor", "achieved": tfs, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tfs / dmma_peak,
-                        # ncu --set full, one launch with every pair active: dram read 272.0 MB + write 212.5 MB
-                        # (profiles/r1_final.md); the algorithmic figure of such a launch is 268 + 268 MB
-                        "traffic": 484.5e6 if full else None,
-                        "peak_source": "measured DMMA (mma.sync.m8n8k4.f64) issue peak on this pool, tools/fp64_peak.cu; "
-                                       "MEASURED_PEAKS.json has no FP64 figure (cuBLAS DGEMM here: 35.5)",
+                        "traffic": None,
+                        "traffic_note": "ncu --set full of one launch with every pair active (4096^2): profiles/r2_k3_full.md; "
+                                        "the live figures here average over partially active launches, so the two are not divided",
+                        "peak_measured_this_run": peaks64,
+                        "peak_source": "larger of cuBLAS DGEMM 8192^3 (torch.matmul f64) and tools/fp64_peak (mma.sync.m8n8k4.f64 "
+                                       "issue rate), both measured in this run; MEASURED_PEAKS.json has no FP64 figure",
                         "kernel": "blk32_update_kernel (X<-XW, Y<-YW for 64-column block pairs; FP64 DMMA tiles, "
                                   "W in shared memory in fragment order, cp.async staged, per-pair column pointer tables)",
                         "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
@@ -533,27 +697,26 @@ def run_svdj(args):
                                 "frac": gbs / peak, "peak_source": peak_src}}
         else:
             roofline = {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
-                        "traffic": 484.7e6 if full else None, "peak_source": peak_src,
+                        "traffic": None, "peak_source": peak_src,
                         "kernel": "blk_update_staged_kernel (X<-XW, Y<-YW; FP64 DMMA tiles, cp.async staged)",
                         "frac_of_8TBps_nominal": gbs / 8000.0, "alg_bytes_per_launch": bytes_per_launch,
                         "avg_launch_us": k_ms * 1e3, "launches_probed": int(launches),
                         "fp64_tensor": {"flops_per_launch": flops_per_launch, "achieved_tflops": tfs,
-                                        "peak_tflops": dmma_peak,
-                                        "peak_source": "measured DMMA issue peak, profiles/r1_fp64_peaks.md"}}
+                                        "peak_tflops": dmma_peak, "peak_measured_this_run": peaks64}}
     else:
         # level-1 path: the fused Gram + rotation step is the only kernel of the sweep loop
         alg_bytes = float(np.mean([algorithmic_bytes(m, n, s_.tested, s_.applied) for s_ in stats]))
         achieved = alg_bytes / sweep_s / 1e9
         launches_per_solve = last.step_kernel_launches
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": 478.6e6 if (m, n) == (4096, 4096) else None, "peak_source": peak_src,
+                    "traffic": None, "traffic_note": "ncu capture: profiles/r1_level1_4096.md", "peak_source": peak_src,
                     "kernel": "l1_pair_reg_kernel (fused Gram+rotation step)",
                     "frac_of_8TBps_nominal": achieved / 8000.0,
                     "alg_bytes_per_launch": alg_bytes / max(launches_per_solve, 1),
                     "avg_launch_us": sweep_s / max(launches_per_solve, 1) * 1e6}
 
     # e2e: host buffers (pinned), H2D + solve + D2H inside the timed call
-    hA0 = torch.from_numpy(np.ascontiguousarray(A0.T)).pin_memory()
+    hA0 = dA0.cpu().pin_memory()
     hA = torch.empty_like(hA0).pin_memory()
     hs = torch.zeros(n, dtype=torch.float64).pin_memory()
     hV = torch.empty(n, n, dtype=torch.float64).pin_memory()
@@ -576,31 +739,28 @@ def run_svdj(args):
         e2e_s = float(t.item())
 
     if rank == 0:
-        # accuracy of the last e2e result (cheap, on the GPU) so that the line carries its own parity evidence
-        U = hA.cuda().T
-        V = hV.cuda().T
-        S = hs.cuda()
-        eye = torch.eye(n, dtype=torch.float64, device="cuda")
-        A0d = dA0.T
-        acc = {"orth_u": float((U.T @ U - eye).abs().max()), "orth_v": float((V.T @ V - eye).abs().max()),
-               "resid": float(torch.linalg.norm(A0d - (U * S) @ V.T) / torch.linalg.norm(A0d)),
-               "bound_10_n_eps": 10 * n * 2.0 ** -52}
-        del U, V, eye
-        cpu = cpu_baseline_port(A0, SWEEPS_TO_CONVERGE.get(n, last.sweeps)) if not args.no_cpu_baseline else None
+        # accuracy of the last e2e result, outside every timed region, so that the line carries its own parity
+        # evidence: BASELINE.json's three 10 n eps bounds and sigma against an independent solver
+        sigma_ref, ref_name = (sigma_true, "prescribed spectrum") if sigma_true is not None else lapack_sigma(dA0, n)
+        acc = accuracy_block(dA0.T, hA.cuda().T, hs.cuda(), hV.cuda().T, n, sigma_ref, ref_name)
+        cpu = (cpu_baseline_port(A0, sweeps_to_converge(n, last.sweeps))
+               if not (args.no_cpu_baseline or args.graded) else None)
         pairs = n * (n - 1) // 2
         line = {
             "metric": METRIC, "value": per_step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": False,
             "scaling": "strong" if world == 1 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence",
+            "config": {"workload": workload,
                        "variant": {1: "level1", 2: "block"}.get(last.variant, str(last.variant)),
                        "block_width": int(last.reserved) if last.variant == svdj.VARIANT_BLOCK else None,
-                       "tol": "m*2^-53 relative", "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20)
+                       "precondition": int(last.precondition),
+                       "tol": "sqrt(m)*2^-53 relative (LAPACK dgesvj)", "l2": "inputs_larger_than_l2 (A+V = %d MiB)" % (2 * m * n * 8 >> 20)
                        if 2 * m * n * 8 > 126e6 else "inputs fit L2; restored from a master copy each step",
                        "parallelism": "1 GPU" if world == 1 else f"{world} independent replicas"},
             "sweeps": last.sweeps, "rotations_applied": last.applied, "pairs_tested": last.tested,
             "rotations_per_s": last.tested / last.seconds_sweeps,
             "seconds_sweeps": sweep_s, "seconds_finalize": last.seconds_finalize,
+            "seconds_precond": last.seconds_precond,
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
                     "d2h_bytes_per_step": (m * n + n * n + min(m, n)) * 8,
@@ -608,9 +768,10 @@ def run_svdj(args):
             "gpu_launches": int(sum(s_.launches for s_ in stats)),
             "clocks": clocks, "accuracy": acc,
         }
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+        print(json.dumps(line), flush=True)
+        if not acc["ok"]:
+            print("bench.py: accuracy bound violated", file=sys.stderr)
+            return 3
     return 0
 
 
@@ -619,15 +780,28 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="svdj", choices=["svdj", "reference"])
+    ap.add_argument("--impl", default="svdj", choices=["svdj", "reference", "cusolver"])
+    ap.add_argument("--config", type=int, default=0, help="BASELINE.json config: 2 = 4096^2 uniform (default), 3 = 16384^2 "
+                    "uniform, 4 = 1048576 x 512 N(0,1) sharded by rows, 5 = 8192^2 cond 1e12 with two QR steps")
+    ap.add_argument("--graded", action="store_true", help="prescribed geometric spectrum, cond 1e12 (config 5's input)")
+    ap.add_argument("--precondition", type=int, default=-1, help="svdj_opts.precondition: 0, 1, 2; -1 = library decides")
     ap.add_argument("--size", "--n", dest="n", type=int, default=4096)
     ap.add_argument("--rows", type=int, default=0, help="M >= 8 * size: the tall M x size workload, sharded by rows over the GPUs")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"], help="N > 1: how column blocks move")
     args = ap.parse_args()
+    if args.config == 3:
+        args.n = 16384
+    elif args.config == 4:
+        args.rows, args.n = 1048576, 512
+    elif args.config == 5:
+        args.n, args.graded = 8192, True
+        if args.precondition < 0:
+            args.precondition = 2
     if args.impl == "reference":
         return run_reference(args)
+    if args.impl == "cusolver":
+        return run_cusolver(args)
     return run_svdj(args)
 
 

@@ -250,7 +250,8 @@ int svdj_dgesvd_rows_device(int jobu, int jobv, size_t m_local, size_t n, double
  *   collective: every rank calls with the same sizes, jobs and options; only rank 0's A, s, V are used, the other
  *   ranks may pass NULL.  A rank that waits more than 60 s
  *   (SVDJ_MG_TIMEOUT_S) for a peer gives up with SVDJ_ERR_CUDA instead of hanging its GPU.
- * opts->precondition is not applied here (the QR front-end is single-GPU: factor on one GPU first if needed).
+ *   opts->precondition = 1 / 2 works here too: rank 0 factors on its GPU, the ring iterates on the n x n triangular
+ *   factor, rank 0 applies Q; "library decides" (< 0) means no front-end in the multi-GPU entry points.
  * svdj_mg_plan: host-side copy of the tournament the driver walks, for tests: after `round` moves, which block
  *   (0 .. 2P-1) rank r holds as top / bottom and in which of its four buffers, and the transfers of the next move as
  *   (src rank, src buffer, dst rank, dst buffer) quadruples (at most 2P-2).  It stands where the reference's

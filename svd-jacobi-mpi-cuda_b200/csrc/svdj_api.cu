@@ -468,57 +468,20 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
 // ---------------------------------------------------------------------------------------------------------
 static size_t round16(size_t x) { return (x + 15) & ~size_t(15); }
 
-static int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
-                         size_t ldv, int qr_steps, const svdj_opts &o, svdj_stats &st, cudaStream_t stream) {
+// `inner` runs the Jacobi iteration on the n x n factor (the single-GPU sweep loop, or the multi-GPU driver's
+// collective solve on rank 0).  It is called exactly once, even when the QR part failed (pre_status != 0), because
+// a collective inner solve has other ranks waiting for it.
+int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV, size_t ldv,
+                  int qr_steps, const svdj_opts &o, svdj_stats &st, cudaStream_t stream, const InnerSolve &inner) {
   const bool want_u = (jobu != SVDJ_NOVEC), want_v = (jobv != SVDJ_NOVEC);
   Event e0, e1, e2, e3;
-  if (int rc = e0.create()) return rc;
-  if (int rc = e1.create()) return rc;
-  if (int rc = e2.create()) return rc;
-  if (int rc = e3.create()) return rc;
-  SVDJ_CUDA_TRY(cudaEventRecord(e0.e, stream));
-  unsigned long long launches = 0;
-
-  // 1. column norms -> permutation (n doubles to the host and n indices back)
   DevBuf d_norms, d_perm, d_Y, d_T1, d_T2, d_qrs, d_L, d_B1, d_J;
-  if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
-  if (int rc = d_perm.alloc(sizeof(unsigned) * n)) return rc;
-  if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
-  std::vector<double> hn(n);
-  SVDJ_CUDA_TRY(cudaMemcpyAsync(hn.data(), d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
-  SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
-  std::vector<unsigned> perm(n);
-  std::iota(perm.begin(), perm.end(), 0u);
-  std::stable_sort(perm.begin(), perm.end(), [&hn](unsigned x, unsigned y) { return hn[x] > hn[y]; });
-  SVDJ_CUDA_TRY(cudaMemcpyAsync(d_perm.p, perm.data(), sizeof(unsigned) * n, cudaMemcpyHostToDevice, stream));
-
-  // 2. Y = A P, factored in place
+  unsigned long long launches = 0;
   const size_t ldy = round16(m);
   const size_t np = qr_num_panels(n);
-  if (int rc = d_Y.alloc(sizeof(double) * ldy * n)) return rc;
-  if (int rc = d_T1.alloc(sizeof(double) * 1024 * np)) return rc;
-  if (int rc = d_qrs.alloc(qr_scratch_bytes(n))) return rc;
-  if (int rc = launch_gather_columns(dA, lda, d_Y.as<double>(), ldy, m, n, d_perm.as<unsigned>(), nullptr, 0, stream))
-    return rc;
-  launches += 2;
-  if (int rc = qr_factor(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), d_qrs.p, stream, &launches)) return rc;
-
-  // 3. L = R^T (n x n lower triangular, one zero pad row when n is odd so that the vectorised kernels apply)
+  // L = R^T: n x n lower triangular, one zero pad row when n is odd so that the vectorised kernels apply
   const size_t rows_l = (n + 1) & ~size_t(1);
   const size_t ldl = round16(rows_l);
-  if (int rc = d_L.alloc(sizeof(double) * ldl * n)) return rc;
-  if (qr_steps >= 2) {
-    if (int rc = d_B1.alloc(sizeof(double) * ldl * n)) return rc;
-    if (int rc = d_T2.alloc(sizeof(double) * 1024 * np)) return rc;
-    if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_B1.as<double>(), ldl, n, stream)) return rc;
-    if (int rc = qr_factor(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), d_qrs.p, stream, &launches)) return rc;
-    if (int rc = qr_transpose_r(d_B1.as<double>(), ldl, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
-    launches += 2;
-  } else {
-    if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
-    launches += 1;
-  }
-
   // Where the Jacobi iteration accumulates its rotations J.  steps = 1: J becomes U after Q1 is applied, so it grows
   // in the top n rows of the caller's A (whose contents now live in Y); steps = 2: J becomes V after Q2, in a
   // work buffer.
@@ -526,25 +489,70 @@ static int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, siz
   size_t ldj = 0, jrows = n;
   const bool need_j = (qr_steps >= 2) ? want_v : want_u;
   const bool need_w = (qr_steps >= 2) ? want_u : want_v;
-  if (qr_steps >= 2) {
-    if (need_j) {
-      if (int rc = d_J.alloc(sizeof(double) * ldl * n)) return rc;
-      J = d_J.as<double>();
-      ldj = ldl;
-      jrows = rows_l;
+
+  auto prepare = [&]() -> int {
+    if (int rc = e0.create()) return rc;
+    if (int rc = e1.create()) return rc;
+    if (int rc = e2.create()) return rc;
+    if (int rc = e3.create()) return rc;
+    SVDJ_CUDA_TRY(cudaEventRecord(e0.e, stream));
+    // 1. column norms -> permutation (n doubles to the host and n indices back)
+    if (int rc = d_norms.alloc(sizeof(double) * n)) return rc;
+    if (int rc = d_perm.alloc(sizeof(unsigned) * n)) return rc;
+    if (int rc = launch_column_norms(dA, lda, m, n, d_norms.as<double>(), stream)) return rc;
+    std::vector<double> hn(n);
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(hn.data(), d_norms.p, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));
+    std::vector<unsigned> perm(n);
+    std::iota(perm.begin(), perm.end(), 0u);
+    std::stable_sort(perm.begin(), perm.end(), [&hn](unsigned x, unsigned y) { return hn[x] > hn[y]; });
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(d_perm.p, perm.data(), sizeof(unsigned) * n, cudaMemcpyHostToDevice, stream));
+    // 2. Y = A P, factored in place
+    if (int rc = d_Y.alloc(sizeof(double) * ldy * n)) return rc;
+    if (int rc = d_T1.alloc(sizeof(double) * 1024 * np)) return rc;
+    if (int rc = d_qrs.alloc(qr_scratch_bytes(n))) return rc;
+    if (int rc = launch_gather_columns(dA, lda, d_Y.as<double>(), ldy, m, n, d_perm.as<unsigned>(), nullptr, 0, stream))
+      return rc;
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));  // perm (host) must outlive its upload
+    launches += 2;
+    if (int rc = qr_factor(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), d_qrs.p, stream, &launches)) return rc;
+    // 3. L = R^T
+    if (int rc = d_L.alloc(sizeof(double) * ldl * n)) return rc;
+    if (qr_steps >= 2) {
+      if (int rc = d_B1.alloc(sizeof(double) * ldl * n)) return rc;
+      if (int rc = d_T2.alloc(sizeof(double) * 1024 * np)) return rc;
+      if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_B1.as<double>(), ldl, n, stream)) return rc;
+      if (int rc = qr_factor(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), d_qrs.p, stream, &launches)) return rc;
+      if (int rc = qr_transpose_r(d_B1.as<double>(), ldl, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
+      launches += 2;
+    } else {
+      if (int rc = qr_transpose_r(d_Y.as<double>(), ldy, n, d_L.as<double>(), ldl, rows_l, stream)) return rc;
+      launches += 1;
     }
-  } else if (need_j) {
-    SVDJ_CUDA_TRY(cudaMemset2DAsync(dA, lda * sizeof(double), 0, m * sizeof(double), n, stream));
-    J = dA;
-    ldj = lda;
-    jrows = (m >= rows_l) ? rows_l : n;
-  }
-  SVDJ_CUDA_TRY(cudaEventRecord(e1.e, stream));
+    if (qr_steps >= 2) {
+      if (need_j) {
+        if (int rc = d_J.alloc(sizeof(double) * ldl * n)) return rc;
+        J = d_J.as<double>();
+        ldj = ldl;
+        jrows = rows_l;
+      }
+    } else if (need_j) {
+      SVDJ_CUDA_TRY(cudaMemset2DAsync(dA, lda * sizeof(double), 0, m * sizeof(double), n, stream));
+      J = dA;
+      ldj = lda;
+      jrows = (m >= rows_l) ? rows_l : n;
+    }
+    SVDJ_CUDA_TRY(cudaEventRecord(e1.e, stream));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(stream));  // a collective inner solve starts from finished data
+    return SVDJ_OK;
+  };
+  const int pre = prepare();
 
   svdj_opts oi = o;
   oi.precondition = 0;
-  const int rc_inner = solve_on_device(need_w ? SVDJ_ALLVEC : SVDJ_NOVEC, need_j ? SVDJ_ALLVEC : SVDJ_NOVEC, rows_l, n,
-                                       d_L.as<double>(), ldl, ds, J, ldj, need_j ? jrows : n, oi, st, stream);
+  const int rc_inner = inner(pre, need_w ? SVDJ_ALLVEC : SVDJ_NOVEC, need_j ? SVDJ_ALLVEC : SVDJ_NOVEC, rows_l, n,
+                             d_L.as<double>(), ldl, ds, J, ldj, need_j ? jrows : n, oi, st);
+  if (pre != SVDJ_OK) return pre;
   if (rc_inner != SVDJ_OK && rc_inner != SVDJ_NOT_CONVERGED) return rc_inner;
   SVDJ_CUDA_TRY(cudaEventRecord(e2.e, stream));
 
@@ -583,7 +591,7 @@ static int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, siz
 }
 
 // Which front-end runs.  opts.precondition: 0 none, 1 / 2 QR steps, < 0 the library decides.  SVDJ_PRECOND overrides.
-static int precondition_steps(const svdj_opts &o, size_t m, size_t n) {
+int precondition_steps(const svdj_opts &o, size_t m, size_t n) {
   int want = o.precondition;
   if (const char *env = std::getenv("SVDJ_PRECOND")) want = std::atoi(env);
   const bool possible = m >= n && n >= 64 && qr_supported(m, n) && o.threshold_mode == SVDJ_THRESH_REL;
@@ -596,7 +604,12 @@ static int solve_entry(int jobu, int jobv, size_t m, size_t n, double *dA, size_
                        size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st, cudaStream_t stream) {
   const int steps = (m == 0 || n == 0) ? 0 : precondition_steps(o, m, n);
   if (steps == 0) return solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, vrows, o, st, stream);
-  return solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, o, st, stream);
+  return solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, o, st, stream,
+                       [stream](int pre, int ju, int jv, size_t mi, size_t ni, double *A, size_t la, double *s, double *V,
+                                size_t lv, size_t vr, const svdj_opts &oi, svdj_stats &sti) -> int {
+                         if (pre != SVDJ_OK) return pre;
+                         return solve_on_device(ju, jv, mi, ni, A, la, s, V, lv, vr, oi, sti, stream);
+                       });
 }
 
 }  // namespace svdj

@@ -316,6 +316,16 @@ struct BlockProbe {
   cudaEvent_t before = nullptr, after = nullptr;
   unsigned long long *active_pairs = nullptr;
 };
+// A pool of probes a multi-step driver hands out to every 8th step (the events are read back once per sweep)
+struct ProbeSet {
+  BlockProbe *probes = nullptr;
+  int count = 0, used = 0;
+  unsigned long long steps_seen = 0;
+  const BlockProbe *next() {
+    if (probes == nullptr || (steps_seen++ % 8) != 0 || used >= count) return nullptr;
+    return &probes[used++];
+  }
+};
 unsigned blk_num_blocks(size_t n);
 // scratch of a step over nb column blocks (nb as the launcher will see it, padding included)
 void blk_scratch_sizes(size_t m, unsigned nb, size_t *gpart_doubles, size_t *w_doubles, size_t *flag_ints);
@@ -338,7 +348,8 @@ double default_tol(size_t m, int jobu, int jobv);
 int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
                double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
                unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
-               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches);
+               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches,
+               ProbeSet *probes = nullptr);
 
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0 = 0);

@@ -1,6 +1,7 @@
 // svdj_host.cuh -- host-side helpers shared by the drivers (svdj_api.cu, svdj_mg.cu): pooled buffers, RAII wrappers
 #pragma once
 
+#include <functional>
 #include <mutex>
 #include <vector>
 
@@ -140,6 +141,16 @@ struct DeviceGuard {
     if (active) cudaSetDevice(prev);
   }
 };
+
+// The QR-preconditioned solve (svdj_api.cu).  inner(pre_status, jobu, jobv, m, n, A, lda, s, V, ldv, vrows, opts,
+// stats) runs the Jacobi iteration on the triangular factor; it is called exactly once.
+typedef std::function<int(int, int, int, size_t, size_t, double *, size_t, double *, double *, size_t, size_t,
+                          const svdj_opts &, svdj_stats &)>
+    InnerSolve;
+int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV, size_t ldv,
+                  int qr_steps, const svdj_opts &o, svdj_stats &st, cudaStream_t stream, const InnerSolve &inner);
+// QR steps that opts ask for on an m x n problem (0 when the front-end does not apply)
+int precondition_steps(const svdj_opts &o, size_t m, size_t n);
 
 void mg_release_team();  // svdj_mg.cu: tears down the cached ranks of svdj_dgesvd_mg
 

@@ -399,6 +399,10 @@ struct MgRank {
   double *d_sigma = nullptr;                  // 2 w_max
   const double **d_src = nullptr;             // root: gather tables (2 x max_n pointers)
   std::map<std::pair<size_t, size_t>, void *> workspaces;  // (m, 2w) -> RingWorkspace
+  // probes of the update kernel (every 8th step), read back once per sweep
+  static constexpr int kProbes = 192;
+  std::vector<BlockProbe> probe_store;
+  u64 *d_probe_pairs = nullptr;
   u64 epoch = 0;        // solves done (start / done / sigma stamps)
   u64 round_stamp = 0;  // rounds done
   u64 sweep_stamp = 0;  // sweeps done
@@ -432,6 +436,11 @@ static void mg_destroy(MgRank *R) {
   if (R->d_mail_ptrs[1]) cudaFree(R->d_mail_ptrs[1]);
   if (R->d_sigma) cudaFree(R->d_sigma);
   if (R->d_src) cudaFree(R->d_src);
+  if (R->d_probe_pairs) cudaFree(R->d_probe_pairs);
+  for (BlockProbe &pb : R->probe_store) {
+    if (pb.before) cudaEventDestroy(pb.before);
+    if (pb.after) cudaEventDestroy(pb.after);
+  }
   if (R->stream) cudaStreamDestroy(R->stream);
   cudaGetLastError();
   delete R;
@@ -474,6 +483,13 @@ static int mg_alloc_local(MgRank *R) {
   if (e == cudaSuccess) e = cudaMalloc(&R->d_mail_ptrs[1], sizeof(u64 *) * P);
   if (e == cudaSuccess) e = cudaMalloc(&R->d_sigma, sizeof(double) * 2 * R->w_max);
   if (e == cudaSuccess && R->rank == 0) e = cudaMalloc(&R->d_src, sizeof(double *) * 2 * npad);
+  if (e == cudaSuccess) e = cudaMalloc(&R->d_probe_pairs, sizeof(u64));
+  R->probe_store.assign(MgRank::kProbes, BlockProbe());
+  for (int i = 0; i < MgRank::kProbes && e == cudaSuccess; ++i) {
+    e = cudaEventCreate(&R->probe_store[i].before);
+    if (e == cudaSuccess) e = cudaEventCreate(&R->probe_store[i].after);
+    R->probe_store[i].active_pairs = R->d_probe_pairs;
+  }
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     set_error("svdj_mg: set-up allocation failed on rank %d: %s", R->rank, cudaGetErrorString(e));
@@ -702,6 +718,12 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   MG_TRY(svdj_ring_ws_set_floor(ws, floor_norm));
 
   // ---- sweeps ----
+  ProbeSet ps;
+  ps.probes = R->probe_store.data();
+  ps.count = (int)R->probe_store.size();
+  double probe_ms = 0.0;
+  unsigned long long probe_launches = 0;
+  SVDJ_CUDA_TRY(cudaMemsetAsync(R->d_probe_pairs, 0, sizeof(u64), s));
   SVDJ_CUDA_TRY(cudaEventRecord(ev0.e, s));
   const int rounds = 2 * P - 1;
   const bool rotate_v = want_v;
@@ -723,7 +745,7 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
                         rotate_v ? 1 : 0, rd == 0 ? SVDJ_PHASE_ALL : SVDJ_PHASE_CROSS, o.tol, inner,
                         reinterpret_cast<unsigned long long *>(R->d_counters), s, dst_top ? R->A_of(dst_top) : nullptr,
                         dst_bot ? R->A_of(dst_bot) : nullptr, dst_top ? R->V_of(dst_top) : nullptr,
-                        dst_bot ? R->V_of(dst_bot) : nullptr, P > 1, &launches));
+                        dst_bot ? R->V_of(dst_bot) : nullptr, P > 1, &launches, &ps));
       if (P > 1) {
         const u64 stamp = ++R->round_stamp;
         u64 *sig[2] = {nullptr, nullptr};
@@ -766,6 +788,12 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
                 code & 0xffffffffffffull);
       return SVDJ_ERR_CUDA;
     }
+    for (int i = 0; i < ps.used; ++i) {
+      float pms = 0.f;
+      if (cudaEventElapsedTime(&pms, ps.probes[i].before, ps.probes[i].after) == cudaSuccess) probe_ms += pms;
+    }
+    probe_launches += (unsigned long long)ps.used;
+    ps.used = 0;
     st.sweeps = sweep + 1;
     st.applied += R->h_out[0];
     double off;
@@ -879,6 +907,14 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   float ms = 0.f;
   SVDJ_CUDA_TRY(cudaEventElapsedTime(&ms, ev0.e, ev1.e));
   st.seconds_sweeps = ms * 1e-3;
+  {  // the update kernel on THIS rank: mean probed launch and the block pairs those launches updated
+    u64 pairs = 0;
+    SVDJ_CUDA_TRY(cudaMemcpyAsync(&pairs, R->d_probe_pairs, sizeof(u64), cudaMemcpyDeviceToHost, s));
+    SVDJ_CUDA_TRY(cudaStreamSynchronize(s));
+    st.step_kernel_ms = probe_launches ? probe_ms / (double)probe_launches : 0.0;
+    st.step_kernel_launches = probe_launches;
+    st.probe_block_pairs = pairs;
+  }
   st.launches += launches;
   st.variant = SVDJ_VARIANT_BLOCK;
   st.reserved = (w % 32 == 0) ? 32 : 16;
@@ -976,7 +1012,30 @@ static int rank_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, 
   SVDJ_CUDA_TRY(cudaGetDevice(&cur));
   if (cur != R->device) SVDJ_CUDA_TRY(cudaSetDevice(R->device));
   const svdj_opts o = mg_opts(opts, m, jobu, jobv);
-  const int rc = mg_solve_device(R, jobu, jobv, m, n, dA, lda, ds, dV, ldv, o, st, pre_status);
+  // QR front-end (opts.precondition = 1 or 2; "library decides" means none here): rank 0 factors on its GPU, the
+  // ring iterates on the n x n triangular factor, rank 0 maps the result back.  Every rank works out the same
+  // inner sizes from the same arguments.
+  svdj_opts oq = o;
+  if (oq.precondition < 0) oq.precondition = 0;
+  const int steps = precondition_steps(oq, m, n);
+  int rc;
+  if (steps == 0) {
+    rc = mg_solve_device(R, jobu, jobv, m, n, dA, lda, ds, dV, ldv, o, st, pre_status);
+  } else {
+    const size_t rows_l = (n + 1) & ~size_t(1);
+    const bool want_u = jobu != SVDJ_NOVEC, want_v = jobv != SVDJ_NOVEC;
+    const bool need_j = steps >= 2 ? want_v : want_u, need_w = steps >= 2 ? want_u : want_v;
+    if (R->rank == 0 && pre_status == SVDJ_OK) {
+      rc = solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, oq, st, R->stream,
+                         [R](int pre, int ju, int jv, size_t mi, size_t ni, double *A, size_t la, double *s, double *V,
+                             size_t lv, size_t, const svdj_opts &oi, svdj_stats &sti) -> int {
+                           return mg_solve_device(R, ju, jv, mi, ni, A, la, s, V, lv, oi, sti, pre);
+                         });
+    } else {
+      rc = mg_solve_device(R, need_w ? SVDJ_ALLVEC : SVDJ_NOVEC, need_j ? SVDJ_ALLVEC : SVDJ_NOVEC, rows_l, n, nullptr, 0,
+                           nullptr, nullptr, 0, o, st, pre_status);
+    }
+  }
   if (cur != R->device && cur >= 0) cudaSetDevice(cur);
   return rc;
 }

@@ -94,7 +94,8 @@ namespace svdj {
 int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, double *dA_right, size_t lda,
                double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
                unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
-               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches) {
+               double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches,
+               ProbeSet *probes) {
   RingWorkspace *W = static_cast<RingWorkspace *>(ws);
   if (W == nullptr) return -1;
   if (m == 0 || m != W->m) return -2;
@@ -149,7 +150,9 @@ int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, doub
       b.V2_st = dstV_right ? dstV_right : dV_right;
       b.force_update = 1;
     }
-    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, launches, nullptr, nullptr)) return rc;
+    if (int rc = (wide ? blk32_launch_step : blk_launch_step)(b, k, W->gpart, W->wbuf, W->wflag, st, launches,
+                                                                    probes ? probes->next() : nullptr, nullptr))
+      return rc;
   }
   return SVDJ_OK;
 }
