@@ -69,7 +69,7 @@ def _check_cli_output(tmp_path, out):
     mr = re.fullmatch(r"\|\|A-USVt\|\|_F: ([0-9.e+-]+)", lines[2])                 # main.cu:1665
     assert mr
     # the input is the reference's own upper-triangular seed-1000000 matrix; |A|_F ~ 209
-    assert float(mr.group(1)) <= 1e-12 * 512
+    assert float(mr.group(1)) <= 10 * 512 * H.EPS * 210.0
     reports = glob.glob(os.path.join(tmp_path, "reporte-dimension-512-time-*.txt"))        # main.cu:1667
     assert len(reports) == 1
     assert re.fullmatch(r"reporte-dimension-512-time-\d\d-\d\d-\d{4}-\d\d-\d\d-\d\d\.txt", os.path.basename(reports[0]))

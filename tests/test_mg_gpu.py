@@ -79,6 +79,22 @@ def test_mg_rank_deficient_and_novec(svdj, devices):
     assert H.sigma_error_normwise(s2, sl) <= 1e-12
 
 
+@pytest.mark.parametrize("steps", [1, 2])
+@pytest.mark.parametrize("devices", _device_lists(2))
+def test_mg_graded_spectrum_with_qr_front_end(svdj, devices, steps):
+    """cond 1e12 (config 5's construction at n = 512) on the ring: rank 0 factors, the ring iterates on R^T."""
+    n = 512
+    A0, sigma = H.prescribed_spectrum(n, 1e12, seed=5)
+    A = A0.copy(order="F"); s = np.zeros(n); V = np.zeros((n, n), order="F")
+    st = svdj.dgesvd_mg(svdj.AllVec, svdj.AllVec, n, n, A, n, s, V, n, len(devices), devices,
+                        opts=svdj.default_opts(precondition=steps))
+    assert st.converged == 1 and st.precondition == steps and st.sweeps <= 18
+    assert H.sigma_error_normwise(s, sigma) <= 1e-12
+    q = H.svd_quality(A0, A, s, V)
+    bound = 10 * n * H.EPS
+    assert q["orth_u"] <= bound and q["orth_v"] <= bound and q["resid"] <= bound, q
+
+
 def test_mg_argument_errors(svdj):
     A = np.zeros((64, 64), order="F"); s = np.zeros(64); V = np.zeros((64, 64), order="F")
     with pytest.raises(svdj.SvdjError):

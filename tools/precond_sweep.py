@@ -13,6 +13,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--sizes", type=int, nargs="*", default=[2048, 4096])
 ap.add_argument("--graded", type=int, nargs="*", default=[4096, 8192])
 ap.add_argument("--steps", type=int, nargs="*", default=[0, 1, 2])
+ap.add_argument("--cluster", action="store_true", help="graded inputs: n/8 equal singular values from index n/4")
 a = ap.parse_args()
 svdj = importlib.import_module("svd-jacobi-mpi-cuda_b200")
 dev = torch.device("cuda")
@@ -47,8 +48,10 @@ for n in a.graded:
     Q1, _ = torch.linalg.qr(torch.randn(n, n, dtype=torch.float64, device=dev, generator=g))
     Q2, _ = torch.linalg.qr(torch.randn(n, n, dtype=torch.float64, device=dev, generator=g))
     sig = torch.logspace(0, -12, n, dtype=torch.float64, device=dev)
+    if a.cluster:
+        sig[n // 4: n // 4 + n // 8] = sig[n // 4]
     A0 = ((Q1 * sig) @ Q2.T).T.contiguous(); del Q1, Q2
     for s in a.steps:
         if s == 0 and n > 4096:
             continue
-        run(f"{n}x{n} graded cond 1e12", A0, sig, s)
+        run(f"{n}x{n} graded cond 1e12" + (" clustered" if a.cluster else ""), A0, torch.sort(sig, descending=True).values, s)
