@@ -298,19 +298,27 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     double wp0 = (w1 == l2) ? 1.0 : 0.0, wq0 = 0.0, wp1 = 0.0, wq1 = (w1 == l2) ? 1.0 : 0.0;
     double(*X)[kE32Stride] = G1;  // rows 0..31: g21 of thread (row, lane); rows 32..63: g22
     const int up = (l2 + 1) & 31, wdst = (w1 + 31) & 31, ldst = (l2 + 31) & 31;
+    // Software pipeline.  The rotations of step t+1 depend only on the G update of step t, not on its W update: so
+    // a step is  [G update, post the next rotation inputs, hand the bottom rows on]  barrier  [warp 0: the 32
+    // rotations of step t+1  ||  warps 1..31: W update of step t, column shifts, fetch the new bottom rows]  barrier.
+    // The W update (a third of the arithmetic, two thirds of the shuffles) runs under warp 0's latency chain
+    // (threshold test, two rsqrt) instead of after it; warp 0 does its own W update last.
+    auto rotations = [&]() -> int {  // warp 0, lane = pair index: from rin_* to rot_c / rot_s; returns how many rotate
+      const double al = rin_al[l2], be = rin_be[l2], ga = rin_ga[l2];
+      const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
+      double c = 1.0, sn = 0.0;
+      if (rot) fast_rotation(al, be, ga, c, sn);
+      rot_c[l2] = c;
+      rot_s[l2] = sn;
+      return __popc(__ballot_sync(0xffffffffu, rot));
+    };
+    int pending = 0;  // warp 0: rotations of the step about to run
+    if (w1 == 0) pending = rotations();
+    __syncthreads();
     for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
       int sweep_rot = 0;  // counted by warp 0
       for (int t = 0; t < 32; ++t) {
-        if (w1 == 0) {
-          const double al = rin_al[l2], be = rin_be[l2], ga = rin_ga[l2];
-          const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
-          double c = 1.0, sn = 0.0;
-          if (rot) fast_rotation(al, be, ga, c, sn);
-          rot_c[l2] = c;
-          rot_s[l2] = sn;
-          sweep_rot += __popc(__ballot_sync(0xffffffffu, rot));
-        }
-        __syncthreads();
+        sweep_rot += pending;
         const double c2 = rot_c[l2], s2 = rot_s[l2], c1 = rot_c[w1], s1 = rot_s[w1];
         const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
         const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
@@ -330,15 +338,17 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
         X[wdst][l2] = n21;
         X[32 + wdst][ldst] = n22;
         g11 = n11;
+        __syncthreads();  // everybody has read rot_* of this step; rin_* and X of the next are complete
+        if (w1 == 0) pending = rotations();  // (after the last step of the last sweep it is simply not used)
         g12 = __shfl_sync(0xffffffffu, n12, up);
         const double nq0 = s2 * wp0 + c2 * wq0, nq1 = s2 * wp1 + c2 * wq1;
         wp0 = c2 * wp0 - s2 * wq0;
         wp1 = c2 * wp1 - s2 * wq1;
         wq0 = __shfl_sync(0xffffffffu, nq0, up);
         wq1 = __shfl_sync(0xffffffffu, nq1, up);
-        __syncthreads();
         g21 = X[w1][l2];
         g22 = X[32 + w1][l2];
+        __syncthreads();
       }
       if (tid == 0) sweep_rot_s = sweep_rot;
       __syncthreads();
