@@ -69,7 +69,9 @@ typedef struct svdj_opts {
   int device;         /* CUDA device ordinal; < 0 = the calling thread's current device */
   int precondition;   /* QR front-end before the sweeps (m >= n >= 64): 0 none; 1: de Rijk column sort, A P = Q R by
                          blocked Householder, Jacobi on R^T; 2: R^T factored once more (strongly graded spectra);
-                         < 0: the library decides (default).  All on the device, this library's own kernels */
+                         < 0 (default): plain sweeps first; if 26 of them have not converged (a strongly graded
+                         spectrum), the solve starts again from a saved copy of A with two QR steps.  All on the
+                         device, this library's own kernels */
 } svdj_opts;
 
 typedef struct svdj_stats {

@@ -26,7 +26,7 @@ namespace svdj {
 
 static thread_local char g_error[512] = "";
 
-// What opts.precondition < 0 resolves to (DESIGN.md section 5 has the measurements behind it)
+// What opts.precondition < 0 resolves to where no second attempt is possible (see solve_entry)
 static constexpr int kAutoPrecondition = 0;
 
 void set_error(const char *fmt, ...) {
@@ -557,10 +557,11 @@ int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda
   SVDJ_CUDA_TRY(cudaEventRecord(e2.e, stream));
 
   // 4. back to the caller's U and V
+  void *rsc = static_cast<char *>(d_qrs.p) + 0;  // qr_apply_q reuses the factorisation's scratch (sized for n columns)
   double *W = d_L.as<double>();  // normalised columns of L J: the left singular vectors of L, sigma-sorted
   if (qr_steps >= 2) {
     if (want_v) {  // V = P (Q2 J)
-      if (int rc = qr_apply_q(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), J, ldj, n, stream, &launches)) return rc;
+      if (int rc = qr_apply_q(d_B1.as<double>(), ldl, n, n, d_T2.as<double>(), J, ldj, n, rsc, stream, &launches)) return rc;
       if (int rc = qr_scatter_rows(J, ldj, dV, ldv, n, n, d_perm.as<unsigned>(), stream)) return rc;
       launches += 1;
     }
@@ -568,7 +569,7 @@ int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda
       SVDJ_CUDA_TRY(cudaMemset2DAsync(dA, lda * sizeof(double), 0, m * sizeof(double), n, stream));
       SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dA, lda * sizeof(double), W, ldl * sizeof(double), n * sizeof(double), n,
                                       cudaMemcpyDeviceToDevice, stream));
-      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, stream, &launches)) return rc;
+      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, rsc, stream, &launches)) return rc;
     }
   } else {
     if (want_v) {  // V = P W
@@ -576,7 +577,7 @@ int solve_with_qr(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda
       launches += 1;
     }
     if (want_u) {  // U = Q1 [J; 0], in place
-      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, stream, &launches)) return rc;
+      if (int rc = qr_apply_q(d_Y.as<double>(), ldy, m, n, d_T1.as<double>(), dA, lda, n, rsc, stream, &launches)) return rc;
     }
   }
   SVDJ_CUDA_TRY(cudaEventRecord(e3.e, stream));
@@ -600,16 +601,59 @@ int precondition_steps(const svdj_opts &o, size_t m, size_t n) {
   return want > 2 ? 2 : want;
 }
 
+static const InnerSolve &single_gpu_inner(cudaStream_t stream) {
+  static thread_local InnerSolve f;
+  f = [stream](int pre, int ju, int jv, size_t mi, size_t ni, double *A, size_t la, double *s, double *V, size_t lv,
+               size_t vr, const svdj_opts &oi, svdj_stats &sti) -> int {
+    if (pre != SVDJ_OK) return pre;
+    return solve_on_device(ju, jv, mi, ni, A, la, s, V, lv, vr, oi, sti, stream);
+  };
+  return f;
+}
+
+// opts.precondition < 0 ("the library decides").  Measured (profiles/r2_precond.md): on dense random inputs the QR
+// front-end costs about what the two sweeps it saves are worth (4096^2: 0.389 s with, 0.384 s without), so it is not
+// run up front.  What it is indispensable for are strongly graded spectra, which cannot be told from the columns
+// beforehand and on which plain Jacobi crawls (8192^2, cond 1e12: not converged after 60 sweeps).  So: sweep the raw
+// columns, and if kAutoGiveUpSweeps sweeps -- more than any regular input has needed up to 16384^2 (19) -- have not
+// converged, start again from a saved copy of A with two QR steps.  The copy costs one m x n buffer.
+static constexpr int kAutoGiveUpSweeps = 26;
+
 static int solve_entry(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
                        size_t ldv, size_t vrows, const svdj_opts &o, svdj_stats &st, cudaStream_t stream) {
-  const int steps = (m == 0 || n == 0) ? 0 : precondition_steps(o, m, n);
+  if (m == 0 || n == 0) return solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, vrows, o, st, stream);
+  svdj_opts probe = o;
+  probe.precondition = 2;
+  const bool qr_possible = precondition_steps(probe, m, n) == 2;
+  const bool automatic = o.precondition < 0 && std::getenv("SVDJ_PRECOND") == nullptr;
+  if (automatic && qr_possible && o.max_sweeps > kAutoGiveUpSweeps) {
+    DevBuf copy;
+    if (int rc = copy.alloc(sizeof(double) * m * n)) return rc;
+    SVDJ_CUDA_TRY(cudaMemcpy2DAsync(copy.p, m * sizeof(double), dA, lda * sizeof(double), m * sizeof(double), n,
+                                    cudaMemcpyDeviceToDevice, stream));
+    svdj_opts first = o;
+    first.precondition = 0;
+    first.max_sweeps = kAutoGiveUpSweeps;
+    const int rc1 = solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, vrows, first, st, stream);
+    if (rc1 != SVDJ_NOT_CONVERGED) return rc1;
+    // start again, preconditioned
+    const svdj_stats tried = st;
+    SVDJ_CUDA_TRY(cudaMemcpy2DAsync(dA, lda * sizeof(double), copy.p, m * sizeof(double), m * sizeof(double), n,
+                                    cudaMemcpyDeviceToDevice, stream));
+    std::memset(&st, 0, sizeof(st));
+    svdj_opts second = o;
+    second.precondition = 2;
+    const int rc2 = solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, 2, second, st, stream, single_gpu_inner(stream));
+    st.sweeps += tried.sweeps;  // the abandoned attempt is part of what this call cost
+    st.tested += tried.tested;
+    st.applied += tried.applied;
+    st.launches += tried.launches;
+    st.seconds_sweeps += tried.seconds_sweeps;
+    return rc2;
+  }
+  const int steps = precondition_steps(o, m, n);
   if (steps == 0) return solve_on_device(jobu, jobv, m, n, dA, lda, ds, dV, ldv, vrows, o, st, stream);
-  return solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, o, st, stream,
-                       [stream](int pre, int ju, int jv, size_t mi, size_t ni, double *A, size_t la, double *s, double *V,
-                                size_t lv, size_t vr, const svdj_opts &oi, svdj_stats &sti) -> int {
-                         if (pre != SVDJ_OK) return pre;
-                         return solve_on_device(ju, jv, mi, ni, A, la, s, V, lv, vr, oi, sti, stream);
-                       });
+  return solve_with_qr(jobu, jobv, m, n, dA, lda, ds, dV, ldv, steps, o, st, stream, single_gpu_inner(stream));
 }
 
 }  // namespace svdj
@@ -742,7 +786,12 @@ int svdj_qr_apply_q_device(size_t m, size_t n, const double *dY, size_t ld, cons
   if (dC == nullptr && m * ncols > 0) return -6;
   if (ldc < m) return -7;
   if (ncols > 0x7fffffffu) return -8;
-  return qr_apply_q(dY, ld, m, n, dT, dC, ldc, ncols, static_cast<cudaStream_t>(stream), nullptr);
+  DevBuf scratch;
+  if (int rc = scratch.alloc(qr_scratch_bytes(ncols))) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int rc = qr_apply_q(dY, ld, m, n, dT, dC, ldc, ncols, scratch.p, st, nullptr)) return rc;
+  SVDJ_CUDA_TRY(cudaStreamSynchronize(st));  // the scratch goes back to the pool on return
+  return SVDJ_OK;
 }
 
 int svdj_dgesvd_device(int jobu, int jobv, size_t m, size_t n, double *dA, size_t lda, double *ds, double *dV,
