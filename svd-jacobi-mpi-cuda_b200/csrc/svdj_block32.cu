@@ -151,12 +151,13 @@ __global__ void __launch_bounds__(128) blk32_gram_kernel(const BlockArgs a, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// K2: eigen-decomposition of the 64 x 64 Gram matrix, cyclic two-sided Jacobi in shared memory, 1024 threads:
+// K2: eigen-decomposition of the 64 x 64 Gram matrix, cyclic two-sided Jacobi in shared memory, 512 threads:
 // warp j1, lane j2 owns the 2 x 2 block G[{p1,q1}][{p2,q2}]; each warp computes the 32 rotations of a step in
 // its 32 lanes (lane = pair index) and fetches its own row rotation by shuffle; one barrier per step.
 // ------------------------------------------------------------------------------------------------
 static constexpr int kE32Stride = kD64 + 2;  // odd (stride - 1): conflict-free rotation inputs, see svdj_block.cu
 static constexpr size_t kE32Smem = sizeof(double) * 5 * kD64 * kE32Stride;
+static constexpr int kE32Threads = 512;  // 16 warps: 128 registers per thread for the 4 x 4 register blocks of the CROSS loop
 
 __device__ __forceinline__ void circle_pair64(int t, int j, int &p, int &q) {
   int x, y;
@@ -173,7 +174,7 @@ __device__ __forceinline__ void circle_pair64(int t, int j, int &p, int &q) {
   q = max(x, y);
 }
 
-__global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
+__global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs a, const unsigned k, const unsigned splits,
                                                          const double *__restrict__ gpart, double *__restrict__ wbuf,
                                                          int *__restrict__ wflag) {
   extern __shared__ __align__(16) double sm[];
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     // rotated Gram blocks the eigen-solves of the blocks' previous pairs left behind (refreshed from the columns
     // themselves in the first step of every sweep, which is also the only step that tests intra-block pairs)
     const Pair bp = block_pair(a, k, pair);
-    for (unsigned i = tid; i < 16 * 64; i += 1024) {
+    for (unsigned i = tid; i < 16 * 64; i += kE32Threads) {
       double s = 0.0;
       for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
       const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
@@ -208,13 +209,13 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       G0[c][r] = s;
     }
     const double *cp = a.gcache + (size_t)bp.p * (kB32 * kB32), *cq = a.gcache + (size_t)bp.q * (kB32 * kB32);
-    {
-      const int r = tid >> 5, c = tid & 31;
-      G0[r][c] = cp[tid];
-      G0[32 + r][32 + c] = cq[tid];
+    for (unsigned i = tid; i < kB32 * kB32; i += kE32Threads) {
+      const int r = i >> 5, c = i & 31;
+      G0[r][c] = cp[i];
+      G0[32 + r][32 + c] = cq[i];
     }
   } else {
-    for (unsigned i = tid; i < kGramPart32; i += 1024) {
+    for (unsigned i = tid; i < kGramPart32; i += kE32Threads) {
       double s = 0.0;
       for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
       const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   }
   const bool cross = a.cross_only != 0;
   if (!cross)  // the CROSS loop keeps W in registers and writes it out at the end
-    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
+    for (unsigned i = tid; i < kD64 * kD64; i += kE32Threads) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
   if (tid == 0) fresh_max = 0ull;
   __syncthreads();
 
@@ -250,9 +251,9 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       }
     };
     if (cross) {
-      look((int)(tid >> 5), 32 + (int)(tid & 31));
+      for (unsigned i = tid; i < kB32 * kB32; i += kE32Threads) look((int)(i >> 5), 32 + (int)(i & 31));
     } else {
-      for (unsigned i = tid; i < kD64 * kD64; i += 1024)
+      for (unsigned i = tid; i < kD64 * kD64; i += kE32Threads)
         if ((i >> 6) < (i & 63)) look((int)(i >> 6), (int)(i & 63));
     }
 #pragma unroll
@@ -280,7 +281,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   int total_rot = 0;
   int cur = 0;
   const int w1 = tid >> 5, l2 = lane;
-  const int nr_t = next_slot(w1), nr_b = next_slot(32 + w1), nc_t = next_slot(l2), nc_b = next_slot(32 + l2);
+  const int nc_t = next_slot(l2), nc_b = next_slot(32 + l2);
   if (cross && tid < 32) {  // rotation inputs of the first CROSS step
     rin_al[tid] = G0[tid][32 + tid];
     rin_be[tid] = G0[tid][tid];
@@ -288,86 +289,176 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
   }
   any = __syncthreads_or(any);
   if (cross && any) {
-    // CROSS schedule with the matrices in registers.  In this schedule the top slots stay and the bottom slots move
-    // down by one per step, so of a thread's 2 x 2 block g11 stays where it is, g12 comes from the next lane
-    // (shuffle), and only the bottom row (g21, g22) changes warps and goes through shared memory; W's rows never
-    // move, so W lives in registers for the whole solve.  (With G and W round-tripping through shared memory the
-    // loop was bound by shared-memory bandwidth: 16 accesses per thread and step, now 4.)  The inputs of the
-    // next step's rotations are posted by the threads that produce them.
-    double g11 = G0[w1][l2], g12 = G0[w1][32 + l2], g21 = G0[32 + w1][l2], g22 = G0[32 + w1][32 + l2];
-    double wp0 = (w1 == l2) ? 1.0 : 0.0, wq0 = 0.0, wp1 = 0.0, wq1 = (w1 == l2) ? 1.0 : 0.0;
-    double(*X)[kE32Stride] = G1;  // rows 0..31: g21 of thread (row, lane); rows 32..63: g22
-    const int up = (l2 + 1) & 31, wdst = (w1 + 31) & 31, ldst = (l2 + 31) & 31;
-    // Software pipeline.  The rotations of step t+1 depend only on the G update of step t, not on its W update: so
-    // a step is  [G update, post the next rotation inputs, hand the bottom rows on]  barrier  [warp 0: the 32
-    // rotations of step t+1  ||  warps 1..31: W update of step t, column shifts, fetch the new bottom rows]  barrier.
-    // The W update (a third of the arithmetic, two thirds of the shuffles) runs under warp 0's latency chain
-    // (threshold test, two rsqrt) instead of after it; warp 0 does its own W update last.
-    auto rotations = [&]() -> int {  // warp 0, lane = pair index: from rin_* to rot_c / rot_s; returns how many rotate
-      const double al = rin_al[l2], be = rin_be[l2], ga = rin_ga[l2];
-      const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
-      double c = 1.0, sn = 0.0;
-      if (rot) fast_rotation(al, be, ga, c, sn);
-      rot_c[l2] = c;
-      rot_s[l2] = sn;
-      return __popc(__ballot_sync(0xffffffffu, rot));
-    };
-    int pending = 0;  // warp 0: rotations of the step about to run
-    if (w1 == 0) pending = rotations();
-    __syncthreads();
-    for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
-      int sweep_rot = 0;  // counted by warp 0
-      for (int t = 0; t < 32; ++t) {
-        sweep_rot += pending;
-        const double c2 = rot_c[l2], s2 = rot_s[l2], c1 = rot_c[w1], s1 = rot_s[w1];
-        const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
-        const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
-        const double n11 = c1 * h11 - s1 * h21;
-        double n21 = s1 * h11 + c1 * h21;
-        double n12 = c1 * h12 - s1 * h22;
-        const double n22 = s1 * h12 + c1 * h22;
-        if (w1 == l2) {
-          if (s1 != 0.0) {
-            n12 = 0.0;  // the rotated pair is orthogonal by construction
-            n21 = 0.0;
-          }
-          rin_be[w1] = n11;    // G[j][j] of the next step, j = w1
-          rin_ga[wdst] = n22;  // G[32+j][32+j] of the next step, j = w1 - 1
+    // CROSS schedule with the matrices in registers, on 9 of the 32 warps.  In this schedule the top slots stay and
+    // the bottom slots move down by one per step.  256 worker threads (warps 0..7) hold G and W as 4 x 4 register
+    // blocks: thread (R, C) owns the row pairs {2R, 2R+1} x the column pairs {2C, 2C+1} of G (each pair = one top and
+    // one bottom slot) and rows {2R, 2R+1, 32+2R, 32+2R+1} of W over the same column slots.  Half of every shift
+    // then stays inside the thread (pair 2R+1 -> pair 2R); the other half comes from the next lane (columns:
+    // shuffle) or the next thread row (rows: shared memory).  Against one 2 x 2 block per thread on 1024 threads this
+    // halves the shared-memory traffic and the barrier width, and gives every thread four independent FMA chains.
+    // Warp 8 does nothing but the 32 rotations of the NEXT step (lane = pair): they depend only on the G update of
+    // this step, so they run while the workers do this step's W update and shifts (software pipeline).
+    // A step:  [workers: G update, post the next rotation inputs, hand the bottom rows on]  barrier
+    //          [warp 8: rotations of step t+1  ||  workers: shifts, W update]  barrier.
+    __shared__ double2 rot_cs[32];
+    __shared__ int total_rot_s;
+    auto bar9 = [] { asm volatile("bar.sync 1, 288;" ::: "memory"); };
+    double(*Xbt)[32] = reinterpret_cast<double(*)[32]>(&G1[0][0]);           // [16 thread rows][32 column pairs]
+    double(*Xbb)[32] = reinterpret_cast<double(*)[32]>(&G1[0][0] + 16 * 32);
+    if (tid >= 256 && tid < 288) {
+      // ---- the rotation warp ----
+      auto rotations = [&]() -> int {
+        const double al = rin_al[lane], be = rin_be[lane], ga = rin_ga[lane];
+        const bool rot = al * al > tol2 * be * ga && be > a.floor2 && ga > a.floor2;
+        double c = 1.0, sn = 0.0;
+        if (rot) fast_rotation(al, be, ga, c, sn);
+        rot_cs[lane] = make_double2(c, sn);
+        return __popc(__ballot_sync(0xffffffffu, rot));
+      };
+      int pending = rotations();
+      int tot = 0;
+      bar9();  // A: rotations of step 0 are in place
+      for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+        int sweep_rot = 0;
+        for (int t = 0; t < 32; ++t) {
+          sweep_rot += pending;
+          bar9();                    // B: the workers have posted rin_* of the next step
+          pending = rotations();
+          bar9();                    // A
         }
-        if (l2 == ((w1 + 1) & 31)) rin_al[w1] = n12;  // G[j][32+j] of the next step, j = w1
-        X[wdst][l2] = n21;
-        X[32 + wdst][ldst] = n22;
-        g11 = n11;
-        __syncthreads();  // everybody has read rot_* of this step; rin_* and X of the next are complete
-        if (w1 == 0) pending = rotations();  // (after the last step of the last sweep it is simply not used)
-        g12 = __shfl_sync(0xffffffffu, n12, up);
-        const double nq0 = s2 * wp0 + c2 * wq0, nq1 = s2 * wp1 + c2 * wq1;
-        wp0 = c2 * wp0 - s2 * wq0;
-        wp1 = c2 * wp1 - s2 * wq1;
-        wq0 = __shfl_sync(0xffffffffu, nq0, up);
-        wq1 = __shfl_sync(0xffffffffu, nq1, up);
-        g21 = X[w1][l2];
-        g22 = X[32 + w1][l2];
-        __syncthreads();
+        if (lane == 0) sweep_rot_s = sweep_rot;
+        tot += sweep_rot;
+        bar9();
+        if (sweep_rot == 0) break;
       }
-      if (tid == 0) sweep_rot_s = sweep_rot;
-      __syncthreads();
-      const int sr = sweep_rot_s;
-      total_rot += sr;
-      if (sr == 0) break;
+      if (lane == 0) total_rot_s = tot;
+    } else if (tid < 256) {
+      // ---- the workers ----
+      const int R = (int)(tid >> 4), C = (int)(tid & 15);
+      const int upl = (int)(lane & 16u) | ((C + 1) & 15);  // lane of thread (R, C + 1)
+      const int Rdn = (R + 15) & 15;                        // the thread row that takes over our pair 2R
+      double gtt[2][2], gtb[2][2], gbt[2][2], gbb[2][2];
+      double wt[4][2], wb[4][2];                            // W rows {2R, 2R+1, 32+2R, 32+2R+1} x column pairs
+#pragma unroll
+      for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+          const int ra = 2 * R + ia, cb = 2 * C + ib;
+          gtt[ia][ib] = G0[ra][cb];
+          gtb[ia][ib] = G0[ra][32 + cb];
+          gbt[ia][ib] = G0[32 + ra][cb];
+          gbb[ia][ib] = G0[32 + ra][32 + cb];
+        }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+          const int wrow = 2 * R + (r & 1) + 32 * (r >> 1), cb = 2 * C + ib;
+          wt[r][ib] = (wrow == cb) ? 1.0 : 0.0;
+          wb[r][ib] = (wrow == 32 + cb) ? 1.0 : 0.0;
+        }
+      bar9();  // A
+      for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
+        for (int t = 0; t < 32; ++t) {
+          double2 rc[2], rr[2];
+          rc[0] = rot_cs[2 * C];
+          rc[1] = rot_cs[2 * C + 1];
+          rr[0] = rot_cs[2 * R];
+          rr[1] = rot_cs[2 * R + 1];
+          double ntt[2][2], ntb[2][2], nbt[2][2], nbb[2][2];
+#pragma unroll
+          for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 2; ++ib) {
+              const double c2 = rc[ib].x, s2 = rc[ib].y, c1 = rr[ia].x, s1 = rr[ia].y;
+              const double h11 = c2 * gtt[ia][ib] - s2 * gtb[ia][ib], h12 = s2 * gtt[ia][ib] + c2 * gtb[ia][ib];
+              const double h21 = c2 * gbt[ia][ib] - s2 * gbb[ia][ib], h22 = s2 * gbt[ia][ib] + c2 * gbb[ia][ib];
+              ntt[ia][ib] = c1 * h11 - s1 * h21;
+              nbt[ia][ib] = s1 * h11 + c1 * h21;
+              ntb[ia][ib] = c1 * h12 - s1 * h22;
+              nbb[ia][ib] = s1 * h12 + c1 * h22;
+              const int ra = 2 * R + ia, cb = 2 * C + ib;
+              if (ra == cb) {
+                if (s1 != 0.0) {
+                  ntb[ia][ib] = 0.0;  // the rotated pair is orthogonal by construction
+                  nbt[ia][ib] = 0.0;
+                }
+                rin_be[ra] = ntt[ia][ib];              // G[j][j] of the next step, j = ra
+                rin_ga[(ra + 31) & 31] = nbb[ia][ib];  // G[32+j][32+j] of the next step, j = ra - 1
+              }
+              if (cb == ((ra + 1) & 31)) rin_al[ra] = ntb[ia][ib];  // G[j][32+j] of the next step, j = ra
+            }
+          // the bottom row of our pair 2R goes to thread row R - 1 (as its pair 2R - 1), bottom columns already
+          // shifted: column pair cb lands on cb - 1
+          *reinterpret_cast<double2 *>(&Xbt[Rdn][2 * C]) = make_double2(nbt[0][0], nbt[0][1]);
+          Xbb[Rdn][(2 * C + 31) & 31] = nbb[0][0];
+          Xbb[Rdn][2 * C] = nbb[0][1];
+          bar9();  // B: everybody has read rot_cs of this step; rin_* and X of the next are complete
+          // ---- shifts and the W update, under the rotation warp's latency chain ----
+          // top rows: bottom column (b) <- column pair + 1
+#pragma unroll
+          for (int ia = 0; ia < 2; ++ia) {
+            gtt[ia][0] = ntt[ia][0];
+            gtt[ia][1] = ntt[ia][1];
+            gtb[ia][0] = ntb[ia][1];
+            gtb[ia][1] = __shfl_sync(0xffffffffu, ntb[ia][0], upl);
+          }
+          // bottom row of pair 2R <- bottom row of pair 2R + 1 (own), with the column shift
+          gbt[0][0] = nbt[1][0];
+          gbt[0][1] = nbt[1][1];
+          gbb[0][0] = nbb[1][1];
+          gbb[0][1] = __shfl_sync(0xffffffffu, nbb[1][0], upl);
+          // W: columns rotate with the column pairs; the bottom column shifts like G's
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            double nwb[2];
+#pragma unroll
+            for (int ib = 0; ib < 2; ++ib) {
+              const double c2 = rc[ib].x, s2 = rc[ib].y;
+              nwb[ib] = s2 * wt[r][ib] + c2 * wb[r][ib];
+              wt[r][ib] = c2 * wt[r][ib] - s2 * wb[r][ib];
+            }
+            wb[r][0] = nwb[1];
+            wb[r][1] = __shfl_sync(0xffffffffu, nwb[0], upl);
+          }
+          // bottom row of pair 2R + 1 <- thread row R + 1
+          {
+            const double2 xt = *reinterpret_cast<const double2 *>(&Xbt[R][2 * C]);
+            const double2 xb = *reinterpret_cast<const double2 *>(&Xbb[R][2 * C]);
+            gbt[1][0] = xt.x;
+            gbt[1][1] = xt.y;
+            gbb[1][0] = xb.x;
+            gbb[1][1] = xb.y;
+          }
+          bar9();  // A: rot_cs of the next step is in place; X may be rewritten
+        }
+        bar9();
+        if (sweep_rot_s == 0) break;
+      }
+#pragma unroll
+      for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+          const int ra = 2 * R + ia, cb = 2 * C + ib;
+          G0[ra][cb] = gtt[ia][ib];
+          G0[ra][32 + cb] = gtb[ia][ib];
+          G0[32 + ra][cb] = gbt[ia][ib];
+          G0[32 + ra][32 + cb] = gbb[ia][ib];
+        }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int ib = 0; ib < 2; ++ib) {
+          const int wrow = 2 * R + (r & 1) + 32 * (r >> 1), cb = 2 * C + ib;
+          W[wrow][cb] = wt[r][ib];
+          W[wrow][32 + cb] = wb[r][ib];
+        }
     }
-    G0[w1][l2] = g11;
-    G0[w1][32 + l2] = g12;
-    G0[32 + w1][l2] = g21;
-    G0[32 + w1][32 + l2] = g22;
-    W[w1][l2] = wp0;
-    W[w1][32 + l2] = wq0;
-    W[w1 + 32][l2] = wp1;
-    W[w1 + 32][32 + l2] = wq1;
     __syncthreads();
+    total_rot += total_rot_s;
   }
   if (cross && !any && a.force_update) {  // W = I still moves the columns (last step of a ring round)
-    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
+    for (unsigned i = tid; i < kD64 * kD64; i += kE32Threads) W[i >> 6][i & 63] = ((i >> 6) == (i & 63)) ? 1.0 : 0.0;
     __syncthreads();
   }
   for (int sw = 0; sw < ((any && !cross) ? a.max_inner_sweeps : 0); ++sw) {
@@ -377,8 +468,20 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
       double(*Gn)[kE32Stride] = cur ? G0 : G1;
       double(*Wc)[kE32Stride] = cur ? W1 : W;
       double(*Wn)[kE32Stride] = cur ? W : W1;
-      const double g11 = Gc[w1][l2], g12 = Gc[w1][32 + l2], g21 = Gc[32 + w1][l2], g22 = Gc[32 + w1][32 + l2];
-      const double wp0 = Wc[w1][l2], wq0 = Wc[w1][32 + l2], wp1 = Wc[w1 + 32][l2], wq1 = Wc[w1 + 32][32 + l2];
+      // every thread works on two 2 x 2 blocks: row pairs warp and warp + 16 (the kernel runs 16 warps)
+      double g11[2], g12[2], g21[2], g22[2], wp0[2], wq0[2], wp1[2], wq1[2];
+#pragma unroll
+      for (int vv = 0; vv < 2; ++vv) {
+        const int wv = w1 + 16 * vv;
+        g11[vv] = Gc[wv][l2];
+        g12[vv] = Gc[wv][32 + l2];
+        g21[vv] = Gc[32 + wv][l2];
+        g22[vv] = Gc[32 + wv][32 + l2];
+        wp0[vv] = Wc[wv][l2];
+        wq0[vv] = Wc[wv][32 + l2];
+        wp1[vv] = Wc[wv + 32][l2];
+        wq1[vv] = Wc[wv + 32][32 + l2];
+      }
       if (w1 == 0) {
         // the 32 rotations of the step, once per CTA (one per lane); with every warp computing them the kernel
         // was bound by instruction issue and the FP64 pipe (~half of its instructions were this arithmetic)
@@ -391,23 +494,29 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
         sweep_rot += __popc(__ballot_sync(0xffffffffu, rot));
       }
       __syncthreads();
-      const double c2 = rot_c[l2], s2 = rot_s[l2], c1 = rot_c[w1], s1 = rot_s[w1];
-      const double h11 = c2 * g11 - s2 * g12, h12 = s2 * g11 + c2 * g12;
-      const double h21 = c2 * g21 - s2 * g22, h22 = s2 * g21 + c2 * g22;
-      double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
-      double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
-      if (w1 == l2 && s1 != 0.0) {
-        n12 = 0.0;  // the rotated pair is orthogonal by construction
-        n21 = 0.0;
+      const double c2 = rot_c[l2], s2 = rot_s[l2];
+#pragma unroll
+      for (int vv = 0; vv < 2; ++vv) {
+        const int wv = w1 + 16 * vv;
+        const int nr_t = next_slot(wv), nr_b = next_slot(32 + wv);
+        const double c1 = rot_c[wv], s1 = rot_s[wv];
+        const double h11 = c2 * g11[vv] - s2 * g12[vv], h12 = s2 * g11[vv] + c2 * g12[vv];
+        const double h21 = c2 * g21[vv] - s2 * g22[vv], h22 = s2 * g21[vv] + c2 * g22[vv];
+        double n11 = c1 * h11 - s1 * h21, n21 = s1 * h11 + c1 * h21;
+        double n12 = c1 * h12 - s1 * h22, n22 = s1 * h12 + c1 * h22;
+        if (wv == l2 && s1 != 0.0) {
+          n12 = 0.0;  // the rotated pair is orthogonal by construction
+          n21 = 0.0;
+        }
+        Gn[nr_t][nc_t] = n11;
+        Gn[nr_t][nc_b] = n12;
+        Gn[nr_b][nc_t] = n21;
+        Gn[nr_b][nc_b] = n22;
+        Wn[wv][nc_t] = c2 * wp0[vv] - s2 * wq0[vv];
+        Wn[wv][nc_b] = s2 * wp0[vv] + c2 * wq0[vv];
+        Wn[wv + 32][nc_t] = c2 * wp1[vv] - s2 * wq1[vv];
+        Wn[wv + 32][nc_b] = s2 * wp1[vv] + c2 * wq1[vv];
       }
-      Gn[nr_t][nc_t] = n11;
-      Gn[nr_t][nc_b] = n12;
-      Gn[nr_b][nc_t] = n21;
-      Gn[nr_b][nc_b] = n22;
-      Wn[w1][nc_t] = c2 * wp0 - s2 * wq0;
-      Wn[w1][nc_b] = s2 * wp0 + c2 * wq0;
-      Wn[w1 + 32][nc_t] = c2 * wp1 - s2 * wq1;
-      Wn[w1 + 32][nc_b] = s2 * wp1 + c2 * wq1;
       cur ^= 1;
       __syncthreads();
     }
@@ -418,7 +527,7 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     if (sr == 0) break;
   }
   if (cur) {  // an odd number of steps was taken: the live copies are G1 / W1; bring W back (G is only read)
-    for (unsigned i = tid; i < kD64 * kD64; i += 1024) W[i >> 6][i & 63] = W1[i >> 6][i & 63];
+    for (unsigned i = tid; i < kD64 * kD64; i += kE32Threads) W[i >> 6][i & 63] = W1[i >> 6][i & 63];
     __syncthreads();
   }
 
@@ -428,8 +537,11 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     // 8 x 16 piece (tile row w >> 2, tile columns 2 (w & 3), +1) of the result.  (As scalar FMAs they were 45 % of
     // this kernel's time, bound by the shared-memory loads: 5 loads per 4 FMAs.)
     const int g = lane >> 2, tg = lane & 3;
-    const int ti = (tid >> 5) >> 2, tj = 2 * ((tid >> 5) & 3);
-    {
+    // (16 warps: warp w computes the pieces of the virtual warps w and w + 16)
+#pragma unroll
+    for (int vv = 0; vv < 2; ++vv) {
+      const int vw = w1 + 16 * vv;
+      const int ti = vw >> 2, tj = 2 * (vw & 3);
       double d0a = 0.0, d0b = 0.0, d1a = 0.0, d1b = 0.0;
 #pragma unroll 4
       for (int ks = 0; ks < 16; ++ks) {
@@ -451,13 +563,12 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     {
       // output slot of every column: eigenvalues descending over the valid slots (single GPU only).  Warp w ranks
       // columns w and 32 + w: lane j compares them with columns j and 32 + j, two ballots each.
-      const int w = tid >> 5;
       const double dj0 = Gc[lane][lane], dj1 = Gc[32 + lane][32 + lane];
       const bool v0 = valid[lane] != 0, v1 = valid[32 + lane] != 0;
       const unsigned vm0 = __ballot_sync(0xffffffffu, v0), vm1 = __ballot_sync(0xffffffffu, v1);
 #pragma unroll
-      for (int hsel = 0; hsel < 2; ++hsel) {
-        const int i = w + 32 * hsel;
+      for (int hsel = 0; hsel < 4; ++hsel) {
+        const int i = w1 + 16 * hsel;  // 16 warps rank 4 columns each
         const double di = Gc[i][i];
         const unsigned b0 = __ballot_sync(0xffffffffu, v0 && (dj0 > di || (dj0 == di && (int)lane < i)));
         const unsigned b1 = __ballot_sync(0xffffffffu, v1 && (dj1 > di || (dj1 == di && 32 + (int)lane < i)));
@@ -475,33 +586,40 @@ __global__ void __launch_bounds__(1024) blk32_eig_kernel(const BlockArgs a, cons
     __syncthreads();
     if (a.gcache != nullptr) {  // the rotated diagonal blocks, in the order the columns are written back in
       const Pair bp = block_pair(a, k, pair);
-      for (unsigned i = tid; i < kD64 * kD64; i += 1024) {
+      for (unsigned i = tid; i < kD64 * kD64; i += kE32Threads) {
         const int orow = rank_of[i >> 6], ocol = rank_of[i & 63];
         if ((orow < 32) == (ocol < 32))
           a.gcache[(size_t)(orow < 32 ? bp.p : bp.q) * (kB32 * kB32) + (orow & 31) * kB32 + (ocol & 31)] =
               Gc[i >> 6][i & 63];
       }
     }
-    double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
-#pragma unroll 4
-    for (int ks = 0; ks < 16; ++ks) {
-      const double af = W[8 * ti + g][4 * ks + tg];
-      dmma884(u0a, u0b, af, T[4 * ks + tg][8 * tj + g]);
-      dmma884(u1a, u1b, af, T[4 * ks + tg][8 * tj + 8 + g]);
-    }
     double *wdst = wbuf + (size_t)pair * kD64 * kD64;  // column-major: wdst[c * 64 + r]
-    const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
-    wdst[rank_of[c] * kD64 + r] = u0a;
-    wdst[rank_of[c + 1] * kD64 + r] = u0b;
-    wdst[rank_of[c + 8] * kD64 + r] = u1a;
-    wdst[rank_of[c + 9] * kD64 + r] = u1b;
+#pragma unroll
+    for (int vv = 0; vv < 2; ++vv) {
+      const int vw = w1 + 16 * vv;
+      const int ti = vw >> 2, tj = 2 * (vw & 3);
+      double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
+#pragma unroll 4
+      for (int ks = 0; ks < 16; ++ks) {
+        const double af = W[8 * ti + g][4 * ks + tg];
+        dmma884(u0a, u0b, af, T[4 * ks + tg][8 * tj + g]);
+        dmma884(u1a, u1b, af, T[4 * ks + tg][8 * tj + 8 + g]);
+      }
+      const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
+      wdst[rank_of[c] * kD64 + r] = u0a;
+      wdst[rank_of[c + 1] * kD64 + r] = u0b;
+      wdst[rank_of[c + 8] * kD64 + r] = u1a;
+      wdst[rank_of[c + 9] * kD64 + r] = u1b;
+    }
   }
   else if (a.gcache != nullptr && a.gram_mode == 1) {  // refresh step, nothing rotated: the fresh diagonal blocks
     const Pair bp = block_pair(a, k, pair);
-    const int r = tid >> 5, c = tid & 31;
     double(*Gc)[kE32Stride] = cur ? G1 : G0;
-    a.gcache[(size_t)bp.p * (kB32 * kB32) + tid] = Gc[r][c];
-    a.gcache[(size_t)bp.q * (kB32 * kB32) + tid] = Gc[32 + r][32 + c];
+    for (unsigned i = tid; i < kB32 * kB32; i += kE32Threads) {
+      const int r = i >> 5, c = i & 31;
+      a.gcache[(size_t)bp.p * (kB32 * kB32) + i] = Gc[r][c];
+      a.gcache[(size_t)bp.q * (kB32 * kB32) + i] = Gc[32 + r][32 + c];
+    }
   }
   if (tid == 0) {
     wflag[pair] = (total_rot > 0 || a.force_update) ? 1 : 0;
@@ -821,7 +939,7 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
     gsplits = 1;
   }
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
-  SVDJ_CUDA_TRY(launch_k(blk32_eig_kernel, dim3(pairs), 1024, kE32Smem, st, a, k, gsplits, gsrc, wbuf, wflag));
+  SVDJ_CUDA_TRY(launch_k(blk32_eig_kernel, dim3(pairs), kE32Threads, kE32Smem, st, a, k, gsplits, gsrc, wbuf, wflag));
   if (probe && probe_kernel == 2) SVDJ_CUDA_TRY(cudaEventRecord(probe->after, st));
   if (probe && probe_kernel == 3) SVDJ_CUDA_TRY(cudaEventRecord(probe->before, st));
   SVDJ_CUDA_TRY(launch_k(blk32_update_kernel, dim3(sm_count * kU32CtasPerSm), kU32Threads, kU32Smem, st, a, k, wbuf, wflag, pairs,
