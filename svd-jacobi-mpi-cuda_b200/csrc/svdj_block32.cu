@@ -837,6 +837,10 @@ static unsigned gram32_splits(size_t m, unsigned pairs) {
   const size_t tiles = (m + kG32Rows - 1) / kG32Rows;
   size_t want = ((size_t)waves * 2 * 148) / (pairs ? pairs : 1);
   if (want < 1) want = 1;
+  // few pairs (a rank of a multi-GPU ring): every split is one more partial matrix the eigen-solve has to add up
+  // (37 dependent loads per thread at 8 pairs), so beyond 16 splits a split must keep at least 4096 rows
+  const size_t cap = tiles / 64 > 16 ? tiles / 64 : 16;
+  if (want > cap) want = cap;
   if (want > tiles) want = tiles;
   if (want > 1024) want = 1024;
   const size_t tiles_per_split = (tiles + want - 1) / want;

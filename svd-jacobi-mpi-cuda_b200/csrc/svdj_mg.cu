@@ -731,8 +731,11 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   bool converged = false;
   std::vector<Role> next;
   std::vector<Transfer> tr;
-  int inner = 0;
-  if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) inner = std::atoi(env);
+  // inner sweeps of the small eigen-solves: the single-GPU driver's policy (svdj_api.cu)
+  int inner = (m >= 8 * n) ? 3 : (n >= 8192) ? 2 : 1;
+  if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) {
+    if (std::atoi(env) > 0) inner = std::atoi(env);
+  }
   for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
     SVDJ_CUDA_TRY(cudaMemsetAsync(R->d_counters, 0, sizeof(SweepCounters), s));
     for (int rd = 0; rd < rounds; ++rd) {
