@@ -140,8 +140,17 @@ class GpuBackend:
             pass
 
     def _count(self, phase):
-        nb = 2 * self.w // 16
+        # three kernels per step; the phase runs 64-column kernels (blocks of 32) when the travelling blocks divide
+        # into them, as csrc/svdj_ring.cu decides, else the 32-column ones (blocks of 16)
+        width = 32 if (self.w % 32 == 0 and os.environ.get("SVDJ_BLOCK") != "16") else 16
+        nb = 2 * self.w // width
         self.launches += 3 * (nb // 2 if phase == PHASE_CROSS else int(self.lib.svdj_num_steps(nb)))
+
+    def set_floor(self, floor_norm: float) -> None:
+        """Columns with a norm <= floor_norm are numerically zero and are never rotated (svdj_ring_ws_set_floor)."""
+        rc = self.lib.svdj_ring_ws_set_floor(self.ws, float(floor_norm))
+        if rc != 0:
+            raise self._err(rc, self._last_error())
 
     def phase(self, top, bottom, phase: int, counters: torch.Tensor) -> None:
         """top/bottom: Block objects; counters: int64[2] on the device."""
@@ -379,7 +388,18 @@ class RingSolver:
         self.top.block_id, self.bottom.block_id = t[self.rank], b[self.rank]
 
     # -- the solve ---------------------------------------------------------------------------------------
+    def _set_zero_column_floor(self) -> None:
+        """tol x (largest column norm of the whole input), as in the single-GPU driver: without it the null columns of
+        a rank-deficient or m < n input keep every sweep rotating (their cosines are rounding noise)."""
+        if not hasattr(self.backend, "set_floor"):
+            return
+        local = torch.stack([blk.A[:, : self.m].norm(dim=1).max() for blk in (self.top, self.bottom)]).max().reshape(1)
+        if self.P > 1:
+            dist.all_reduce(local, op=dist.ReduceOp.MAX, group=self.group)
+        self.backend.set_floor(self.tol * float(local.item()))
+
     def solve(self) -> dict:
+        self._set_zero_column_floor()
         rounds = len(self._arrangements)
         sweeps, converged, applied_total, last_off = 0, False, 0, 0.0
         for sweep in range(self.max_sweeps):

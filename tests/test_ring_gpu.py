@@ -42,6 +42,26 @@ def test_single_rank_ring_solver_on_gpu():
     _check(A0, U.cpu().numpy().T, sigma.cpu().numpy(), V.cpu().numpy().T)
 
 
+def test_ring_solver_rank_deficient_input_converges():
+    """The zero-column floor on the ring (svdj_ring_ws_set_floor): without it the null columns of a rank-deficient
+    input keep every sweep rotating until max_sweeps."""
+    ring = _ring()
+    m, n = 256, 192
+    rng = np.random.default_rng(3)
+    A0 = np.asfortranarray(rng.standard_normal((m, 90)) @ rng.standard_normal((90, n)))
+    dev = torch.device("cuda", 0)
+    solver = ring.RingSolver(m, n, dev)
+    solver.scatter_from_root(torch.from_numpy(np.ascontiguousarray(A0.T)).to(dev))
+    st = solver.solve()
+    assert st["converged"] and st["sweeps"] <= 25, st
+    sigma, order = solver.finalize()
+    s = sigma.cpu().numpy()
+    assert H.sigma_error_normwise(s, np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    U, V = solver.gather_to_root(order)
+    V = V.cpu().numpy().T
+    assert np.abs(V.T @ V - np.eye(n)).max() <= 10 * n * H.EPS
+
+
 @pytest.mark.parametrize("P", [2, 4])
 def test_emulated_tournament_on_one_gpu(P):
     """All P ranks' blocks live on one GPU and the rounds run rank after rank: checks SVDJ_PHASE_CROSS (bipartite
