@@ -298,11 +298,18 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
     // halves the shared-memory traffic and the barrier width, and gives every thread four independent FMA chains.
     // Warp 8 does nothing but the 32 rotations of the NEXT step (lane = pair): they depend only on the G update of
     // this step, so they run while the workers do this step's W update and shifts (software pipeline).
-    // A step:  [workers: G update, post the next rotation inputs, hand the bottom rows on]  barrier
-    //          [warp 8: rotations of step t+1  ||  workers: shifts, W update]  barrier.
+    // A step:  workers: update the blocks that feed the next rotations, post them, ARRIVE (no wait)  ->  warp 8
+    //          starts the rotations of step t+1 while the workers finish the G update, hand the bottom rows on
+    //          (worker-only barrier), shift and update W; one barrier of all nine warps ends the step.
     __shared__ double2 rot_cs[32];
     __shared__ int total_rot_s;
-    auto bar9 = [] { asm volatile("bar.sync 1, 288;" ::: "memory"); };
+    // named barriers: 1 = all 9 warps ("the rotations of the next step are in place"); 2 = the workers ARRIVE (do
+    // not wait) once the next rotation inputs are posted, the rotation warp waits on it; 3 = the workers among
+    // themselves (the bottom rows have been handed on)
+    auto bar_all = [] { asm volatile("bar.sync 1, 288;" ::: "memory"); };
+    auto bar_rin_arrive = [] { asm volatile("bar.arrive 2, 288;" ::: "memory"); };
+    auto bar_rin_wait = [] { asm volatile("bar.sync 2, 288;" ::: "memory"); };
+    auto bar_workers = [] { asm volatile("bar.sync 3, 256;" ::: "memory"); };
     double(*Xbt)[32] = reinterpret_cast<double(*)[32]>(&G1[0][0]);           // [16 thread rows][32 column pairs]
     double(*Xbb)[32] = reinterpret_cast<double(*)[32]>(&G1[0][0] + 16 * 32);
     if (tid >= 256 && tid < 288) {
@@ -317,18 +324,18 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
       };
       int pending = rotations();
       int tot = 0;
-      bar9();  // A: rotations of step 0 are in place
+      bar_all();  // rotations of step 0 are in place
       for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
         int sweep_rot = 0;
         for (int t = 0; t < 32; ++t) {
           sweep_rot += pending;
-          bar9();                    // B: the workers have posted rin_* of the next step
+          bar_rin_wait();            // the workers have posted rin_* of the next step (and read rot_cs of this one)
           pending = rotations();
-          bar9();                    // A
+          bar_all();
         }
         if (lane == 0) sweep_rot_s = sweep_rot;
         tot += sweep_rot;
-        bar9();
+        bar_all();
         if (sweep_rot == 0) break;
       }
       if (lane == 0) total_rot_s = tot;
@@ -357,7 +364,9 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
           wt[r][ib] = (wrow == cb) ? 1.0 : 0.0;
           wb[r][ib] = (wrow == 32 + cb) ? 1.0 : 0.0;
         }
-      bar9();  // A
+      // which of this thread's four blocks feed the next step's rotations (pivot blocks and their right neighbours):
+      // they are on the critical path rotation -> G update -> rotation, so they are updated and posted first
+      bar_all();
       for (int sw = 0; sw < a.max_inner_sweeps; ++sw) {
         for (int t = 0; t < 32; ++t) {
           double2 rc[2], rr[2];
@@ -366,34 +375,39 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
           rr[0] = rot_cs[2 * R];
           rr[1] = rot_cs[2 * R + 1];
           double ntt[2][2], ntb[2][2], nbt[2][2], nbb[2][2];
-#pragma unroll
-          for (int ia = 0; ia < 2; ++ia)
-#pragma unroll
-            for (int ib = 0; ib < 2; ++ib) {
-              const double c2 = rc[ib].x, s2 = rc[ib].y, c1 = rr[ia].x, s1 = rr[ia].y;
-              const double h11 = c2 * gtt[ia][ib] - s2 * gtb[ia][ib], h12 = s2 * gtt[ia][ib] + c2 * gtb[ia][ib];
-              const double h21 = c2 * gbt[ia][ib] - s2 * gbb[ia][ib], h22 = s2 * gbt[ia][ib] + c2 * gbb[ia][ib];
-              ntt[ia][ib] = c1 * h11 - s1 * h21;
-              nbt[ia][ib] = s1 * h11 + c1 * h21;
-              ntb[ia][ib] = c1 * h12 - s1 * h22;
-              nbb[ia][ib] = s1 * h12 + c1 * h22;
-              const int ra = 2 * R + ia, cb = 2 * C + ib;
-              if (ra == cb) {
-                if (s1 != 0.0) {
-                  ntb[ia][ib] = 0.0;  // the rotated pair is orthogonal by construction
-                  nbt[ia][ib] = 0.0;
-                }
-                rin_be[ra] = ntt[ia][ib];              // G[j][j] of the next step, j = ra
-                rin_ga[(ra + 31) & 31] = nbb[ia][ib];  // G[32+j][32+j] of the next step, j = ra - 1
+          auto update_block = [&](int ia, int ib) {
+            const double c2 = rc[ib].x, s2 = rc[ib].y, c1 = rr[ia].x, s1 = rr[ia].y;
+            const double h11 = c2 * gtt[ia][ib] - s2 * gtb[ia][ib], h12 = s2 * gtt[ia][ib] + c2 * gtb[ia][ib];
+            const double h21 = c2 * gbt[ia][ib] - s2 * gbb[ia][ib], h22 = s2 * gbt[ia][ib] + c2 * gbb[ia][ib];
+            ntt[ia][ib] = c1 * h11 - s1 * h21;
+            nbt[ia][ib] = s1 * h11 + c1 * h21;
+            ntb[ia][ib] = c1 * h12 - s1 * h22;
+            nbb[ia][ib] = s1 * h12 + c1 * h22;
+            const int ra = 2 * R + ia, cb = 2 * C + ib;
+            if (ra == cb) {
+              if (s1 != 0.0) {
+                ntb[ia][ib] = 0.0;  // the rotated pair is orthogonal by construction
+                nbt[ia][ib] = 0.0;
               }
-              if (cb == ((ra + 1) & 31)) rin_al[ra] = ntb[ia][ib];  // G[j][32+j] of the next step, j = ra
+              rin_be[ra] = ntt[ia][ib];              // G[j][j] of the next step, j = ra
+              rin_ga[(ra + 31) & 31] = nbb[ia][ib];  // G[32+j][32+j] of the next step, j = ra - 1
             }
+            if (cb == ((ra + 1) & 31)) rin_al[ra] = ntb[ia][ib];  // G[j][32+j] of the next step, j = ra
+          };
+          // blocks (0,0), (1,1), (0,1) hold every rotation input a thread with R == C or C == R + 1 can own
+          // ((1,0) of thread (R, R + 1) is pair (2R+1, 2R+2): posted from the late group of THAT thread only when
+          // C == R + 1, so it goes first there) -- simplest correct rule: everything but one block first
+          update_block(0, 0);
+          update_block(1, 1);
+          update_block(0, 1);
+          if (C == ((R + 1) & 15)) update_block(1, 0);
+          bar_rin_arrive();  // rin_* of the next step are complete; rot_cs of this step is in registers
+          if (C != ((R + 1) & 15)) update_block(1, 0);
           // the bottom row of our pair 2R goes to thread row R - 1 (as its pair 2R - 1), bottom columns already
           // shifted: column pair cb lands on cb - 1
           *reinterpret_cast<double2 *>(&Xbt[Rdn][2 * C]) = make_double2(nbt[0][0], nbt[0][1]);
           Xbb[Rdn][(2 * C + 31) & 31] = nbb[0][0];
           Xbb[Rdn][2 * C] = nbb[0][1];
-          bar9();  // B: everybody has read rot_cs of this step; rin_* and X of the next are complete
           // ---- shifts and the W update, under the rotation warp's latency chain ----
           // top rows: bottom column (b) <- column pair + 1
 #pragma unroll
@@ -421,6 +435,7 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
             wb[r][0] = nwb[1];
             wb[r][1] = __shfl_sync(0xffffffffu, nwb[0], upl);
           }
+          bar_workers();  // every thread row has handed its bottom row on
           // bottom row of pair 2R + 1 <- thread row R + 1
           {
             const double2 xt = *reinterpret_cast<const double2 *>(&Xbt[R][2 * C]);
@@ -430,9 +445,9 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
             gbb[1][0] = xb.x;
             gbb[1][1] = xb.y;
           }
-          bar9();  // A: rot_cs of the next step is in place; X may be rewritten
+          bar_all();  // rot_cs of the next step is in place; X may be rewritten
         }
-        bar9();
+        bar_all();
         if (sweep_rot_s == 0) break;
       }
 #pragma unroll
