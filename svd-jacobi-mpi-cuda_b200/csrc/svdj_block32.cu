@@ -552,23 +552,32 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
     // 8 x 16 piece (tile row w >> 2, tile columns 2 (w & 3), +1) of the result.  (As scalar FMAs they were 45 % of
     // this kernel's time, bound by the shared-memory loads: 5 loads per 4 FMAs.)
     const int g = lane >> 2, tg = lane & 3;
-    // (16 warps: warp w computes the pieces of the virtual warps w and w + 16)
+    // 16 warps, 64 output tiles: warp w owns the 2 x 2 tiles (2 (w >> 2) .. +1) x (2 (w & 3) .. +1): two A- and two
+    // B-fragments feed four DMMAs per k-step
+    const int ti0 = 2 * (w1 >> 2), tj0 = 2 * (w1 & 3);
+    {
+      double d[2][2][2];
 #pragma unroll
-    for (int vv = 0; vv < 2; ++vv) {
-      const int vw = w1 + 16 * vv;
-      const int ti = vw >> 2, tj = 2 * (vw & 3);
-      double d0a = 0.0, d0b = 0.0, d1a = 0.0, d1b = 0.0;
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) d[i][j][0] = d[i][j][1] = 0.0;
 #pragma unroll 4
       for (int ks = 0; ks < 16; ++ks) {
-        const double af = W[4 * ks + tg][8 * ti + g];
-        dmma884(d0a, d0b, af, W[4 * ks + tg][8 * tj + g]);
-        dmma884(d1a, d1b, af, W[4 * ks + tg][8 * tj + 8 + g]);
+        const double a0 = W[4 * ks + tg][8 * ti0 + g], a1 = W[4 * ks + tg][8 * ti0 + 8 + g];
+        const double b0 = W[4 * ks + tg][8 * tj0 + g], b1 = W[4 * ks + tg][8 * tj0 + 8 + g];
+        dmma884(d[0][0][0], d[0][0][1], a0, b0);
+        dmma884(d[0][1][0], d[0][1][1], a0, b1);
+        dmma884(d[1][0][0], d[1][0][1], a1, b0);
+        dmma884(d[1][1][0], d[1][1][1], a1, b1);
       }
-      const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
-      T[r][c] = (r == c ? 1.5 : 0.0) - 0.5 * d0a;
-      T[r][c + 1] = (r == c + 1 ? 1.5 : 0.0) - 0.5 * d0b;
-      T[r][c + 8] = (r == c + 8 ? 1.5 : 0.0) - 0.5 * d1a;
-      T[r][c + 9] = (r == c + 9 ? 1.5 : 0.0) - 0.5 * d1b;
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int r = 8 * (ti0 + i) + g, c = 8 * (tj0 + j) + 2 * tg;
+          T[r][c] = (r == c ? 1.5 : 0.0) - 0.5 * d[i][j][0];
+          T[r][c + 1] = (r == c + 1 ? 1.5 : 0.0) - 0.5 * d[i][j][1];
+        }
     }
     if (tid < kD64) {
       const Pair bp = block_pair(a, k, pair);
@@ -609,22 +618,29 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
       }
     }
     double *wdst = wbuf + (size_t)pair * kD64 * kD64;  // column-major: wdst[c * 64 + r]
+    {
+      double u[2][2][2];
 #pragma unroll
-    for (int vv = 0; vv < 2; ++vv) {
-      const int vw = w1 + 16 * vv;
-      const int ti = vw >> 2, tj = 2 * (vw & 3);
-      double u0a = 0.0, u0b = 0.0, u1a = 0.0, u1b = 0.0;
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) u[i][j][0] = u[i][j][1] = 0.0;
 #pragma unroll 4
       for (int ks = 0; ks < 16; ++ks) {
-        const double af = W[8 * ti + g][4 * ks + tg];
-        dmma884(u0a, u0b, af, T[4 * ks + tg][8 * tj + g]);
-        dmma884(u1a, u1b, af, T[4 * ks + tg][8 * tj + 8 + g]);
+        const double a0 = W[8 * ti0 + g][4 * ks + tg], a1 = W[8 * ti0 + 8 + g][4 * ks + tg];
+        const double b0 = T[4 * ks + tg][8 * tj0 + g], b1 = T[4 * ks + tg][8 * tj0 + 8 + g];
+        dmma884(u[0][0][0], u[0][0][1], a0, b0);
+        dmma884(u[0][1][0], u[0][1][1], a0, b1);
+        dmma884(u[1][0][0], u[1][0][1], a1, b0);
+        dmma884(u[1][1][0], u[1][1][1], a1, b1);
       }
-      const int r = 8 * ti + g, c = 8 * tj + 2 * tg;
-      wdst[rank_of[c] * kD64 + r] = u0a;
-      wdst[rank_of[c + 1] * kD64 + r] = u0b;
-      wdst[rank_of[c + 8] * kD64 + r] = u1a;
-      wdst[rank_of[c + 9] * kD64 + r] = u1b;
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int r = 8 * (ti0 + i) + g, c = 8 * (tj0 + j) + 2 * tg;
+          wdst[rank_of[c] * kD64 + r] = u[i][j][0];
+          wdst[rank_of[c + 1] * kD64 + r] = u[i][j][1];
+        }
     }
   }
   else if (a.gcache != nullptr && a.gram_mode == 1) {  // refresh step, nothing rotated: the fresh diagonal blocks
@@ -909,6 +925,7 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
   // The Gram cache needs every block in a pair of the first step, which refreshes it
   if (a.gcache != nullptr && (a.nb % 2 != 0 || blk_full_inner())) a.gcache = nullptr;
   a.gram_mode = (a.gcache == nullptr) ? 0 : (k == 1 ? 1 : 2);
+
   static DeviceOnce once;  // the shared-memory opt-in is per device
   int sm_count = 148;
   SVDJ_CUDA_TRY(once.run(
