@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) blk_eig_kernel(const BlockArgs a, const u
   const double *src = gpart + (size_t)pair * splits * kGramPart;
   for (unsigned i = tid; i < kGramPart; i += 256) {
     double s = 0.0;
-    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart + i];
+    s = sum_partials(src + i, kGramPart, splits);
     const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
     int ti = 0, rem = t;  // t -> (ti, tj) of the upper triangle: rows of 4, 3, 2, 1 tiles
     while (rem >= 4 - ti) {

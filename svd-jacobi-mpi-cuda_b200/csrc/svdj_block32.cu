@@ -201,8 +201,7 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
     // themselves in the first step of every sweep, which is also the only step that tests intra-block pairs)
     const Pair bp = block_pair(a, k, pair);
     for (unsigned i = tid; i < 16 * 64; i += kE32Threads) {
-      double s = 0.0;
-      for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+      const double s = sum_partials(src + i, kGramPart32, splits);
       const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
       const int r = 8 * (t >> 2) + (l >> 2), c = 32 + 8 * (t & 3) + 2 * (l & 3) + e;
       G0[r][c] = s;
@@ -216,8 +215,7 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
     }
   } else {
     for (unsigned i = tid; i < kGramPart32; i += kE32Threads) {
-      double s = 0.0;
-      for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+      const double s = sum_partials(src + i, kGramPart32, splits);
       const int t = i >> 6, l = (i & 63) >> 1, e = i & 1;
       int ti = 0, rem = t;  // t -> (ti, tj): rows of 8, 7, ..., 1 tiles
       while (rem >= kTG - ti) {
@@ -840,8 +838,7 @@ __global__ void __launch_bounds__(256) blk32_gram_reduce_kernel(const double *__
   const unsigned pair = blockIdx.x;
   const double *src = gpart + (size_t)pair * splits * kGramPart32;
   for (unsigned i = threadIdx.x; i < count; i += 256) {
-    double s = 0.0;
-    for (unsigned sp = 0; sp < splits; ++sp) s += src[(size_t)sp * kGramPart32 + i];
+    const double s = sum_partials(src + i, kGramPart32, splits);
     gred[(size_t)pair * kGramPart32 + i] = s;
   }
 }
