@@ -805,7 +805,9 @@ def main():
     elif args.config == 5:
         args.n, args.graded = 8192, True
         if args.precondition < 0:
-            args.precondition = 2
+            # two QR steps on one GPU (10 sweeps instead of 13 outweigh the second factorisation); on several GPUs
+            # the front-end runs on rank 0 alone while a ring sweep is cheap, so one step wins there
+            args.precondition = 2 if args.gpus <= 1 else 1
     if args.impl == "reference":
         return run_reference(args)
     if args.impl == "cusolver":
