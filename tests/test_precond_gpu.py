@@ -179,3 +179,24 @@ def test_config5_full_size(svdj, cluster):
     assert float((U.T @ U - eye).abs().max()) <= bound
     assert float((V.T @ V - eye).abs().max()) <= bound
     assert float(torch.linalg.norm(A0.T - (U * ds) @ V.T) / torch.linalg.norm(A0)) <= bound
+
+
+def test_config5_full_size_with_default_options(svdj):
+    """The same 8192 x 8192 cond-1e12 input with DEFAULT options (precondition < 0): 26 plain sweeps do not converge,
+    the library starts again from its copy of A with two QR steps, and the caller gets a converged SVD with the stated
+    accuracy (round 1 returned status 1 and |U^T U - I| = 0.13 here)."""
+    n = m = 8192
+    A, sigma = _haar_graded_device(n, 1e12, 1234, False)
+    A0 = A.clone()
+    ds = torch.zeros(n, dtype=torch.float64, device="cuda")
+    dV = torch.empty(n, n, dtype=torch.float64, device="cuda")
+    st = svdj.dgesvd_device(svdj.AllVec, svdj.AllVec, m, n, A.data_ptr(), m, ds.data_ptr(), dV.data_ptr(), n,
+                            svdj.default_opts(), allow_not_converged=True)
+    assert st.converged == 1 and st.precondition == 2 and 26 < st.sweeps <= 26 + 15, (st.sweeps, st.precondition)
+    assert float((ds - sigma).abs().max() / sigma[0]) <= 1e-12
+    U, V = A.T, dV.T
+    eye = torch.eye(n, dtype=torch.float64, device="cuda")
+    bound = 10 * n * H.EPS
+    assert float((U.T @ U - eye).abs().max()) <= bound
+    assert float((V.T @ V - eye).abs().max()) <= bound
+    assert float(torch.linalg.norm(A0.T - (U * ds) @ V.T) / torch.linalg.norm(A0)) <= bound
