@@ -215,12 +215,13 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   b.gpart_capacity = gpart_doubles;
   b.tol = o.tol;
   b.threshold_mode = o.threshold_mode;
-  // One cyclic sweep of the small eigen-solve per visit below n = 8192, two from there on: a converged inner
-  // solve buys no outer sweeps, and below 8192 the eigen-solve's latency chain costs more
-  // than the one or two outer sweeps the second inner sweep saves.  SVDJ_INNER_SWEEPS overrides.
+  // Cyclic sweeps of the small eigen-solve per visit: one below n = 4096, two from there on.  A second inner sweep
+  // costs ~14 us per eigen-solve and saves outer sweeps (4096^2: 14 instead of 17, 0.376 -> 0.346 s; 8192^2: 16
+  // instead of 19); at 1024 and 2048 the two effects cancel (tools/tune_inner.sh).  Round 1 drew the line at 8192:
+  // its eigen-solve loop cost twice as much.  SVDJ_INNER_SWEEPS overrides.
   // Tall inputs (m >= 8 n): the eigen-solve does not grow with m while K1/K3 do, so extra inner sweeps are free
   // and every outer sweep saved counts (1,048,576 x 512: 12 sweeps with one inner sweep, 8 with three).
-  b.max_inner_sweeps = (m >= 8 * n) ? 3 : (n >= 8192) ? 2 : 1;
+  b.max_inner_sweeps = (m >= 8 * n) ? 3 : (n >= 4096) ? 2 : 1;
   // row-sharded: every rank must take the same decisions (they all run the same eigen-solves on the same Gram
   // matrices); the local row count differs between ranks, so nothing may depend on it -- tall by definition
   if (rs) b.max_inner_sweeps = 3;
