@@ -715,8 +715,8 @@ size_t svdj_block_schedule_step(size_t nb, int vranks, size_t step, size_t *pq) 
   for (size_t i = 0; i < pairs; ++i) {
     const Pair pr = two_level ? two_level_pair((unsigned)nb, (unsigned)vranks, (unsigned)step + 1u, (unsigned)i)
                               : sameh_pair((unsigned)nb, (unsigned)step + 1u, (unsigned)i);
-    pq[2 * i] = pr.p;
-    pq[2 * i + 1] = pr.q;
+    pq[2 * i] = pr.p < pr.q ? pr.p : pr.q;  // the lower block index first, as the kernels take them
+    pq[2 * i + 1] = pr.p < pr.q ? pr.q : pr.p;
   }
   return pairs;
 }

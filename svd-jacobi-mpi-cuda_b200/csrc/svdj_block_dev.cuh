@@ -97,7 +97,15 @@ __device__ __forceinline__ double *col_ptr_store(const BlockArgs &a, bool is_a, 
 //            the two super-blocks a (virtual) rank holds after the circle-method move.  Same nb-1 steps and
 //            nb/2 pairs per step as sched 0, every pair once per sweep; it needs fewer sweeps.
 __device__ __forceinline__ Pair block_pair(const BlockArgs &a, unsigned k, unsigned idx) {
-  if (a.sched == 0) return sameh_pair(a.nb, k, idx);
+  if (a.sched == 0) {
+    Pair r = sameh_pair(a.nb, k, idx);
+    if (r.p > r.q) {  // the lower block index first: the eigen-solve orders the columns of a pair towards it
+      const unsigned t = r.p;
+      r.p = r.q;
+      r.q = t;
+    }
+    return r;
+  }
   if (a.sched == 1) {
     const unsigned half = a.nb >> 1;
     Pair r;

@@ -349,7 +349,7 @@ int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, doub
                double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
                unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
                double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches,
-               ProbeSet *probes = nullptr);
+               ProbeSet *probes = nullptr, int sort_cols = 0);
 
 // Finalisation (svdj_finalize.cu)
 int launch_set_identity(double *V, size_t ldv, size_t rows, size_t n, cudaStream_t st, size_t row0 = 0);

@@ -337,6 +337,19 @@ static void advance_roles(int P, const std::vector<Role> &roles, std::vector<Rol
   }
 }
 
+// one move of the circle method on the block ids (the same move advance_roles makes on the buffers)
+static void move_ids(int P, std::vector<int> &top, std::vector<int> &bottom) {
+  if (P == 1) return;
+  std::vector<int> nt(P), nb(P);
+  nt[0] = top[0];
+  nt[1] = bottom[0];
+  for (int r = 2; r < P; ++r) nt[r] = top[r - 1];
+  for (int r = 0; r < P - 1; ++r) nb[r] = bottom[r + 1];
+  nb[P - 1] = top[P - 1];
+  top.swap(nt);
+  bottom.swap(nb);
+}
+
 // block ids (top, bottom) per rank after `round` moves
 static void arrangement(int P, int round, std::vector<int> &top, std::vector<int> &bottom) {
   top.resize(P);
@@ -345,17 +358,7 @@ static void arrangement(int P, int round, std::vector<int> &top, std::vector<int
     top[r] = r;
     bottom[r] = P + r;
   }
-  for (int it = 0; it < round; ++it) {
-    if (P == 1) break;
-    std::vector<int> nt(P), nb(P);
-    nt[0] = top[0];
-    nt[1] = bottom[0];
-    for (int r = 2; r < P; ++r) nt[r] = top[r - 1];
-    for (int r = 0; r < P - 1; ++r) nb[r] = bottom[r + 1];
-    nb[P - 1] = top[P - 1];
-    top.swap(nt);
-    bottom.swap(nb);
-  }
+  for (int it = 0; it < round; ++it) move_ids(P, top, bottom);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -731,13 +734,20 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
   bool converged = false;
   std::vector<Role> next;
   std::vector<Transfer> tr;
-  // Inner sweeps of the small eigen-solves.  On the ring a second inner sweep pays only from n = 8192 (2 GPUs,
-  // 4096^2: 0.240 s with one, 0.266 s with two -- it saves a single outer sweep there, three on one GPU, where the
-  // eigen-solve also orders the columns of a block pair by size)
-  int inner = (m >= 8 * n) ? 3 : (n >= 8192) ? 2 : 1;
+  // Inner sweeps of the small eigen-solves.  On the ring a second inner sweep does not pay up to n = 8192 (2 GPUs:
+  // 4096^2 0.249 s with one, 0.265 s with two; 8192^2 1.46 s against 1.55 s -- it saves at most one outer sweep
+  // there, three on one GPU); 16384^2 was measured with two and stays there.
+  int inner = (m >= 8 * n) ? 3 : (n >= 16384) ? 2 : 1;
   if (const char *env = std::getenv("SVDJ_INNER_SWEEPS")) {
     if (std::atoi(env) > 0) inner = std::atoi(env);
   }
+  // Ordering the columns of a block pair by size (as on one GPU) is off: on the ring it needs the second inner
+  // sweep to save outer sweeps (4096^2, 8 ranks: 14 instead of 17) and the two together cost what they save
+  // (2 GPUs, 4096^2: 0.251 s against 0.249 s; 8192^2: 1.52 s against 1.46 s).  SVDJ_MG_SORT=1 turns it on.
+  int sort_pairs = 0;
+  if (const char *env = std::getenv("SVDJ_MG_SORT")) sort_pairs = std::atoi(env) != 0;
+  std::vector<int> id_top, id_bot;
+  arrangement(P, 0, id_top, id_bot);
   for (int sweep = 0; sweep < o.max_sweeps; ++sweep) {
     SVDJ_CUDA_TRY(cudaMemsetAsync(R->d_counters, 0, sizeof(SweepCounters), s));
     for (int rd = 0; rd < rounds; ++rd) {
@@ -746,11 +756,18 @@ static int mg_solve_device(MgRank *R, int jobu, int jobv, size_t m, size_t n, do
       for (const Transfer &t : tr)
         if (t.src_rank == me) (t.src_buf == roles[me].top ? dst_top : dst_bot) = R->peer_buf[t.dst_rank][t.dst_buf];
       double *top = R->buf[roles[me].top], *bot = R->buf[roles[me].bottom];
+      // the block with the lower global index goes in as "left": the eigen-solve then sends the larger columns of
+      // every pair towards the lower index, the same direction in every round on every rank
+      if (id_top[me] > id_bot[me]) {
+        std::swap(top, bot);
+        std::swap(dst_top, dst_bot);
+      }
       MG_TRY(ring_phase(ws, m, npad, w, R->A_of(top), R->A_of(bot), R->lda, R->V_of(top), R->V_of(bot), R->ldv,
                         rotate_v ? 1 : 0, rd == 0 ? SVDJ_PHASE_ALL : SVDJ_PHASE_CROSS, o.tol, inner,
                         reinterpret_cast<unsigned long long *>(R->d_counters), s, dst_top ? R->A_of(dst_top) : nullptr,
                         dst_bot ? R->A_of(dst_bot) : nullptr, dst_top ? R->V_of(dst_top) : nullptr,
-                        dst_bot ? R->V_of(dst_bot) : nullptr, P > 1, &launches, &ps));
+                        dst_bot ? R->V_of(dst_bot) : nullptr, P > 1, &launches, &ps, sort_pairs));
+      move_ids(P, id_top, id_bot);
       if (P > 1) {
         const u64 stamp = ++R->round_stamp;
         u64 *sig[2] = {nullptr, nullptr};

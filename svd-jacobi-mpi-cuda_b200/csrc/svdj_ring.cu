@@ -95,7 +95,7 @@ int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, doub
                double *dV_left, double *dV_right, size_t ldv, int rotate_v, int phase, double tol, int inner_sweeps,
                unsigned long long *d_counters, void *stream, double *dstA_left, double *dstA_right,
                double *dstV_left, double *dstV_right, bool redirect_last, unsigned long long *launches,
-               ProbeSet *probes) {
+               ProbeSet *probes, int sort_cols) {
   RingWorkspace *W = static_cast<RingWorkspace *>(ws);
   if (W == nullptr) return -1;
   if (m == 0 || m != W->m) return -2;
@@ -122,7 +122,9 @@ int ring_phase(void *ws, size_t m, size_t vrows, size_t w, double *dA_left, doub
   b.V2 = dV_right;
   b.split = (unsigned)w;
   b.sched = (phase == SVDJ_PHASE_CROSS) ? 1 : 0;
-  b.sort_cols = 0;
+  // ordering the columns of a block pair by size is only sound when "left" is the block with the lower global
+  // index in every call (the multi-GPU driver sees to that); the Python ring driver leaves it off
+  b.sort_cols = sort_cols;
   b.tol = tol;
   b.threshold_mode = SVDJ_THRESH_REL;
   b.max_inner_sweeps = inner_sweeps > 0 ? inner_sweeps : 2;

@@ -60,8 +60,7 @@ def test_block_schedule_visits_every_block_pair_once(svdj, nb, vranks):
             key = (min(p, q), max(p, q))
             assert key not in seen
             seen.add(key)
-            if vranks >= 2:
-                assert p < q             # lower block first: the eigenvalue ordering needs a consistent direction
+            assert p < q                 # lower block first: the eigenvalue ordering needs a consistent direction
     assert len(seen) == nb * (nb - 1) // 2
 
 
