@@ -61,6 +61,32 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def nvlink_bytes(dev):
+    """Cumulative NVLink payload bytes (tx, rx) of this rank's GPU, summed over its links, from NVML's throughput
+    counters (field values NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX / _RX, KiB, all links) -- read before and after the
+    timed region; no profiler involved.  None where the driver does not expose them."""
+    try:
+        import pynvml
+        import torch
+
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(torch.cuda.get_device_properties(dev).uuid)).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(dev.index)
+        allscope = 0xFFFFFFFF
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, allscope),
+                                                   (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, allscope)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                return None
+            out.append(int(v.value.ullVal) * 1024)
+        return tuple(out)
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -310,6 +336,31 @@ def bench_input(args, dev):
     return A0, f"{m}x{n} dense uniform(0,1) FP64, full SVD (U, S, V) to convergence", None
 
 
+def nvlink_block(nvl, world, m, n, npad, stats, per_step_s):
+    """NVLink traffic of the timed region: NVML counters summed over the ranks beside what the algorithm moves.
+    Per solve: rank 0 hands out 2N-2 of the 2N column blocks of A and collects the same share of U and V; every
+    round 2N-2 blocks (w columns of A and of V each) change GPU, 2N-1 rounds per sweep."""
+    w = npad // (2 * world)
+    block = 8 * w * (m + npad)
+    rounds = sum(int(s_.sweeps) for s_ in stats) * (2 * world - 1)
+    ring = rounds * (2 * world - 2) * block
+    edge = len(stats) * (2 * world - 2) * 8 * w * (m + m + npad)
+    out = {"alg_bytes": ring + edge, "alg_ring_bytes": ring, "alg_scatter_gather_bytes": edge,
+           "block_bytes": block, "rounds": rounds,
+           "alg_avg_gbs_all_ranks": (ring + edge) / (per_step_s * len(stats)) / 1e9,
+           "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX (payload KiB, all links) read on every rank before and after "
+                     "the timed region; ncu is single-GPU on this pool, so there is no per-kernel nvl* capture"}
+    if nvl[2] == world:
+        out.update({"tx_bytes": nvl[0], "rx_bytes": nvl[1], "tx_over_alg": nvl[0] / max(ring + edge, 1),
+                    "avg_tx_gbs_all_ranks": nvl[0] / (per_step_s * len(stats)) / 1e9})
+    else:
+        out.update({"tx_bytes": None, "rx_bytes": None,
+                    "note": "%d of %d ranks could read their counters (on this pool `nvidia-smi nvlink -gt d` prints "
+                            "N/A for every link: profiles/r2_nvlink_counters.txt); the algorithmic bytes stand alone"
+                            % (nvl[2], world)})
+    return out
+
+
 def run_mg(args, svdj, world, rank, local_rank):
     """N > 1: the same m x n solve on N GPUs (strong scaling) through the in-library C++ driver (csrc/svdj_mg.cu,
     one rank per process): 2N column blocks on a ring, the block move fused into the update kernel (peer stores over
@@ -349,17 +400,23 @@ def run_mg(args, svdj, world, rank, local_rank):
         sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stats = []
+    nvl0 = nvlink_bytes(dev)
     ev0.record()
     for _ in range(args.steps):
         stats.append(one_solve())   # returns with this rank's stream drained
     ev1.record()
     barrier()
+    nvl1 = nvlink_bytes(dev)
     clocks = sampler.stop() if root else None
     t = torch.tensor([ev0.elapsed_time(ev1) * 1e-3], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     per_step_s = float(t.item()) / args.steps
     launches = torch.tensor([sum(int(s_.launches) for s_ in stats)], dtype=torch.int64, device=dev)
     dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+    # NVLink payload bytes of the timed region, all ranks (tx, rx, ranks that could read their counters)
+    nvl = torch.tensor([nvl1[0] - nvl0[0], nvl1[1] - nvl0[1], 1] if nvl0 and nvl1 else [0, 0, 0],
+                       dtype=torch.int64, device=dev)
+    dist.all_reduce(nvl, op=dist.ReduceOp.SUM)
 
     # e2e: A starts in rank 0's pinned host memory and U, s, V end there
     if root:
@@ -421,6 +478,7 @@ def run_mg(args, svdj, world, rank, local_rank):
                          "kernel": "blk32_update_kernel on rank 0 (X<-XW, Y<-YW for 64-column block pairs; last step of a round stores into the neighbour GPU)",
                          "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3, "launches_probed": int(pl)},
             "cpu_baseline": None,
+            "nvlink": nvlink_block(nvl.tolist(), world, m, n, npad, stats, per_step_s),
             "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
                     "d2h_bytes_per_step": (m * n + n * n + n) * 8},
             "gpu_launches": int(launches.item()), "clocks": clocks, "accuracy": acc,
@@ -593,6 +651,7 @@ def run_rows(args, svdj, world, rank, local_rank):
                          "flops_per_launch": flops_per_launch, "avg_launch_us": k_ms * 1e3,
                          "launches_probed": int(launches)},
             "cpu_baseline": None,
+            "nvlink": nvlink_block(nvl.tolist(), world, m, n, npad, stats, per_step_s),
             "e2e": {"value": e2e_s, "unit": UNIT, "h2d_bytes_per_step": m * n * 8,
                     "d2h_bytes_per_step": (m * n + n * n + n) * 8},
             "gpu_launches": int(sum(s_.launches for s_ in stats)) * world, "clocks": clocks, "accuracy": acc,
