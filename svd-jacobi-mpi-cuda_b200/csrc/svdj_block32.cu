@@ -757,13 +757,25 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     }
   };
 
+  // W of a block pair into shared memory, fragment-major: per k-step and half of the output columns, 32 lanes x
+  // (b0, b1) then 32 lanes x (b2, b3): each of the two 128-bit loads of a warp reads 512 contiguous bytes
+  auto load_w = [&](unsigned ap) {
+    const double *w = wbuf + (size_t)active[ap] * kD64 * kD64;
+    for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) {
+      const unsigned lo = i & 1, ln = (i >> 1) & 31, hi = (i >> 6) & 1, ks = (i >> 7) & 15, nh = i >> 11;
+      Wsm[i] = w[(32 * nh + 8 * (2 * hi + lo) + (ln >> 2)) * kD64 + 4 * ks + (ln & 3)];
+    }
+  };
+
   unsigned issued = t0;
   issue_tile(issued, 0);
   ++issued;
   cp_async_commit();
 
   const unsigned rowgroup = warp & 3, nhalf = warp >> 2;
-  unsigned cur_ap = 0xffffffffu, cur_next = 0;
+  // the first pair's W while the first tile is in flight (the barrier at the top of the loop publishes it)
+  unsigned cur_ap = t0 / tpp, cur_next = (cur_ap + 1) * tpp;
+  load_w(cur_ap);
   for (unsigned tau = t0; tau < t1; ++tau) {
     cp_async_wait<0>();
     __syncthreads();  // tile tau has landed; everyone is done with the other stage and with the previous W
@@ -773,16 +785,10 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     }
     cp_async_commit();
 
-    if (tau >= cur_next || cur_ap == 0xffffffffu) {  // CTA-uniform: a new block pair, load its W
+    if (tau >= cur_next) {  // CTA-uniform: a new block pair, load its W (everyone is past the barrier above)
       cur_ap = tau / tpp;
       cur_next = (cur_ap + 1) * tpp;
-      const double *w = wbuf + (size_t)active[cur_ap] * kD64 * kD64;
-      // fragment-major layout: per k-step and half of the output columns, 32 lanes x (b0, b1) then 32 lanes x
-      // (b2, b3): each of the two 128-bit loads of a warp reads 512 contiguous bytes
-      for (unsigned i = threadIdx.x; i < kD64 * kD64; i += kU32Threads) {
-        const unsigned lo = i & 1, ln = (i >> 1) & 31, hi = (i >> 6) & 1, ks = (i >> 7) & 15, nh = i >> 11;
-        Wsm[i] = w[(32 * nh + 8 * (2 * hi + lo) + (ln >> 2)) * kD64 + 4 * ks + (ln & 3)];
-      }
+      load_w(cur_ap);
       __syncthreads();
     }
     const unsigned t = tau - cur_ap * tpp;
@@ -790,6 +796,9 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
     const unsigned limit = isa ? a.m : a.vrows;
     const unsigned row0 = (isa ? t : t - tpa) * kU32Rows + 16 * rowgroup;
     const double *tile = tiles + ((tau - t0) & 1) * kU32TileDoubles + 16 * rowgroup + g;
+    // The product is formed transposed -- D' = W^T X^T: W's fragment goes in as the A operand, the tile's as B (the
+    // registers are the same ones either way) -- so that the two accumulator values of a thread are two consecutive
+    // rows of one column: d[h][nt][0..1] = out[row0 + 8h + 2tg, +1][32 nhalf + 8 nt + g], one 16-byte store.
     double d[2][4][2];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) d[0][nt][0] = d[0][nt][1] = d[1][nt][0] = d[1][nt][1] = 0.0;
@@ -799,31 +808,32 @@ __global__ void __launch_bounds__(kU32Threads, kU32CtasPerSm) blk32_update_kerne
       const double a0 = tile[(4 * ks + tg) * kU32Stride];
       const double a1 = tile[(4 * ks + tg) * kU32Stride + 8];
       const double2 b01 = wl[ks * 64], b23 = wl[ks * 64 + 32];
-      dmma884(d[0][0][0], d[0][0][1], a0, b01.x);
-      dmma884(d[1][0][0], d[1][0][1], a1, b01.x);
-      dmma884(d[0][1][0], d[0][1][1], a0, b01.y);
-      dmma884(d[1][1][0], d[1][1][1], a1, b01.y);
-      dmma884(d[0][2][0], d[0][2][1], a0, b23.x);
-      dmma884(d[1][2][0], d[1][2][1], a1, b23.x);
-      dmma884(d[0][3][0], d[0][3][1], a0, b23.y);
-      dmma884(d[1][3][0], d[1][3][1], a1, b23.y);
+      dmma884(d[0][0][0], d[0][0][1], b01.x, a0);
+      dmma884(d[1][0][0], d[1][0][1], b01.x, a1);
+      dmma884(d[0][1][0], d[0][1][1], b01.y, a0);
+      dmma884(d[1][1][0], d[1][1][1], b01.y, a1);
+      dmma884(d[0][2][0], d[0][2][1], b23.x, a0);
+      dmma884(d[1][2][0], d[1][2][1], b23.x, a1);
+      dmma884(d[0][3][0], d[0][3][1], b23.y, a0);
+      dmma884(d[1][3][0], d[1][3][1], b23.y, a1);
     }
-    double *const *stab = coltab[cur_ap & 1u][isa ? 2 : 3] + 32 * nhalf + 2 * tg;
-    double *cst[8];
+    double *const *stab = coltab[cur_ap & 1u][isa ? 2 : 3] + 32 * nhalf + g;
+    double *cst[4];
 #pragma unroll
-    for (int nt = 0; nt < 4; ++nt) {
-      cst[2 * nt] = stab[8 * nt];
-      cst[2 * nt + 1] = stab[8 * nt + 1];
-    }
+    for (int nt = 0; nt < 4; ++nt) cst[nt] = stab[8 * nt];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      const unsigned row = row0 + 8 * h + g;
-      if (row < limit) {
+      const unsigned row = row0 + 8 * h + 2 * tg;
+      if (row + 1 < limit) {
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
-          if (cst[2 * nt] != nullptr) cst[2 * nt][row] = d[h][nt][0];
-          if (cst[2 * nt + 1] != nullptr) cst[2 * nt + 1][row] = d[h][nt][1];
-        }
+        for (int nt = 0; nt < 4; ++nt)
+          if (cst[nt] != nullptr)  // (explicitly global: the pointer comes out of a table, the compiler cannot tell)
+            asm volatile("st.global.v2.f64 [%0], {%1, %2};" ::"l"(cst[nt] + row), "d"(d[h][nt][0]), "d"(d[h][nt][1])
+                         : "memory");
+      } else if (row < limit) {  // odd row count: the last row on its own
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+          if (cst[nt] != nullptr) cst[nt][row] = d[h][nt][0];
       }
     }
   }
@@ -916,6 +926,12 @@ int blk32_launch_step(const BlockArgs &a_in, unsigned k, double *gpart, double *
     double *v2 = a_in.V2_st ? a_in.V2_st : a_in.V2;
     a.V2_st = v2 ? v2 - (size_t)a.split * a.ldv : nullptr;
   }
+  // the update kernel stores two rows at a time
+  for (const double *ptr : {a.A_st, a.A2_st, a.rotate_v ? a.V_st : nullptr, a.rotate_v ? a.V2_st : nullptr})
+    if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) {
+      set_error("block step: a store target is not 16-byte aligned");
+      return -5;
+    }
   // first step of a sweep or ring phase: full eigen-solve (every block is in exactly one pair when their number is
   // even); later steps, and every step of the ring's bipartite CROSS phase: cross pairs only
   a.cross_only = (!blk_full_inner() && (a.sched == 1 || (k > 1 && a.nb % 2 == 0))) ? 1 : 0;
