@@ -289,3 +289,20 @@ def test_quadratic_stop_saves_the_confirming_sweep_only(svdj, monkeypatch):
     s3 = np.zeros(n); V3 = np.zeros((n, n), order="F")
     st3 = svdj.dgesvd(svdj.AllVec, svdj.AllVec, m, n, B, m, s3, V3, n, svdj.default_opts(variant=svdj.VARIANT_BLOCK))
     assert st3.sweeps <= 3 and st3.applied <= 64   # at most a few pairs sitting at the threshold
+
+
+@pytest.mark.parametrize("m,n", [(2880, 336), (512, 2160), (2048, 1160)])
+def test_shapes_whose_padded_block_count_needs_more_scratch(svdj, m, n):
+    """Shapes for which the partial-Gram buffer of round 1 was too small (the number of row splits is not monotonic in
+    the number of block pairs, and the buffer was sized before the block count was padded).  The buffer is now sized
+    from the block count the kernels run with and the launch verifies its capacity: these solve, and solve right."""
+    A0 = H.uniform_matrix(m, n, seed=m + 3 * n)
+    A, s, V, st = _solve(svdj, A0, svdj.VARIANT_AUTO)
+    assert st.converged == 1
+    k = min(m, n)
+    assert H.sigma_error_normwise(s[:k], np.linalg.svd(A0, compute_uv=False)) <= 1e-12
+    bound = 10 * n * H.EPS
+    U = A[:, :k]
+    assert np.abs(U.T @ U - np.eye(k)).max() <= bound
+    assert np.abs(V.T @ V - np.eye(n)).max() <= bound
+    assert np.linalg.norm(A0 - (U * s[:k]) @ V[:, :k].T) <= bound * np.linalg.norm(A0)

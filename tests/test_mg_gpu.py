@@ -101,3 +101,19 @@ def test_mg_argument_errors(svdj):
         svdj.dgesvd_mg(0, 0, 64, 64, A, 64, s, V, 64, 2, [0, 99])
     with pytest.raises(svdj.SvdjError):
         svdj.dgesvd_mg(0, 0, 64, 64, A, 64, s, V, 64, 0)
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_one_process_solves_on_device_0_then_device_1(svdj):
+    """The opt-in shared-memory sizes of the kernels and the SM count are per device: a process that solves on a
+    second GPU through svdj_opts.device must find them set there too (round 1 set them once per process)."""
+    A0 = H.uniform_matrix(640, 384, seed=5)
+    for dev in (0, 1, 0):
+        for variant in (svdj.VARIANT_BLOCK, svdj.VARIANT_LEVEL1):
+            A = A0.copy(order="F")
+            s = np.zeros(384)
+            V = np.zeros((384, 384), order="F")
+            st = svdj.dgesvd(svdj.AllVec, svdj.AllVec, 640, 384, A, 640, s, V, 384,
+                             svdj.default_opts(device=dev, variant=variant))
+            assert st.converged == 1
+            _check(A0, A, s, V)
