@@ -222,6 +222,10 @@ static int solve_on_device(int jobu, int jobv, size_t m, size_t n, double *dA, s
   // Tall inputs (m >= 8 n): the eigen-solve does not grow with m while K1/K3 do, so extra inner sweeps are free
   // and every outer sweep saved counts (1,048,576 x 512: 12 sweeps with one inner sweep, 8 with three).
   b.max_inner_sweeps = (m >= 8 * n) ? 3 : (n >= 4096) ? 2 : 1;
+  // ... and the second one only where the first applied at least 64 of its 1024 rotations: in the last outer sweeps
+  // it finds nothing to do and costs its 14 us all the same (4096^2: 0.346 -> 0.343 s, same 14 sweeps)
+  if (m < 8 * n && b.max_inner_sweeps == 2) b.inner_again = 64;
+  if (const char *env = std::getenv("SVDJ_INNER_AGAIN")) b.inner_again = std::atoi(env) > 0 ? std::atoi(env) : 1;
   // row-sharded: every rank must take the same decisions (they all run the same eigen-solves on the same Gram
   // matrices); the local row count differs between ranks, so nothing may depend on it -- tall by definition
   if (rs) b.max_inner_sweeps = 3;

@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
         if (lane == 0) sweep_rot_s = sweep_rot;
         tot += sweep_rot;
         bar_all();
-        if (sweep_rot == 0) break;
+        if (sweep_rot < a.inner_again) break;
       }
       if (lane == 0) total_rot_s = tot;
     } else if (tid < 256) {
@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(kE32Threads) blk32_eig_kernel(const BlockArgs 
           bar_all();  // rot_cs of the next step is in place; X may be rewritten
         }
         bar_all();
-        if (sweep_rot_s == 0) break;
+        if (sweep_rot_s < a.inner_again) break;
       }
 #pragma unroll
       for (int ia = 0; ia < 2; ++ia)

@@ -268,6 +268,7 @@ struct BlockArgs {
   double tol;
   int threshold_mode;
   int max_inner_sweeps;     // cap on the cyclic sweeps of the 32 x 32 eigen-solve
+  int inner_again = 1;      // another inner sweep only if the last one applied at least this many rotations
   SweepCounters *counters;  // may be null
   double floor2 = 0.0;      // columns with squared norm <= floor2 are treated as zero (never rotated)
   // doubles the caller's partial-Gram buffer holds; the launchers refuse a step that needs more (0 = unchecked)
